@@ -1,0 +1,314 @@
+"""ctypes binding of libacoss_b200.so (the C ABI in include/acoss_b200.h).
+
+This is the only place the package talks to native code.  There is NO fallback: if the
+CUDA library has not been built (``python -m acoss_b200.build``) or there is no usable
+GPU, importing works but creating a context raises.  PyTorch is not needed here; numpy
+arrays are handed over as host pointers.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+DEFAULT_LIB = os.path.join(HERE, "lib", "libacoss_b200.so")
+
+F32, F64 = 0, 1
+FLAG_NO_OTI = 1 << 0
+FLAG_DMAX_CLEAN = 1 << 1
+FLAG_NO_SWAP = 1 << 2
+FLAG_NON_MUTUAL = 1 << 3
+FLAG_WANT_SW = 1 << 4
+
+_c_i32p = ctypes.POINTER(ctypes.c_int32)
+_c_i64p = ctypes.POINTER(ctypes.c_int64)
+_c_u32p = ctypes.POINTER(ctypes.c_uint32)
+_c_u8p = ctypes.POINTER(ctypes.c_uint8)
+_c_f32p = ctypes.POINTER(ctypes.c_float)
+_c_f64p = ctypes.POINTER(ctypes.c_double)
+
+# name -> (restype, argtypes); every symbol include/acoss_b200.h declares
+SIGNATURES = {
+    "acoss_last_error": (ctypes.c_char_p, []),
+    "acoss_version": (ctypes.c_int, []),
+    "acoss_create": (ctypes.c_int, [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int]),
+    "acoss_destroy": (ctypes.c_int, [ctypes.c_void_p]),
+    "acoss_upload_songs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, _c_i64p, _c_i32p,
+                                          ctypes.c_int32, ctypes.c_int32, _c_f64p]),
+    "acoss_serra09_pairs": (ctypes.c_int, [ctypes.c_void_p, _c_i32p, ctypes.c_int64, ctypes.c_int32, ctypes.c_double,
+                                           ctypes.c_uint32, _c_f32p, _c_f32p, _c_f32p, _c_i32p, _c_i32p, _c_u32p,
+                                           _c_i64p, _c_i32p]),
+    "acoss_align_dense": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, _c_i64p, _c_i32p, _c_i32p,
+                                         ctypes.c_int32, ctypes.c_double, ctypes.c_uint32, _c_f32p, _c_u32p, _c_i64p]),
+    "acoss_dp_packed": (ctypes.c_int, [ctypes.c_void_p, _c_u32p, _c_i64p, _c_i32p, _c_i32p, ctypes.c_int32,
+                                       ctypes.c_uint32, _c_f32p]),
+    "acoss_qmax": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p]),
+    "acoss_dmax": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p]),
+    "acoss_qmax_dmax": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p, _c_f32p]),
+    "acoss_swconstrained": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p]),
+    "acoss_kernel_launches": (ctypes.c_int64, [ctypes.c_void_p]),
+    "acoss_reset_counters": (None, [ctypes.c_void_p]),
+    "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
+}
+
+
+class AcossError(RuntimeError):
+    pass
+
+
+def _ptr(arr, typ):
+    return None if arr is None else arr.ctypes.data_as(typ)
+
+
+def load_library(path: str | None = None) -> ctypes.CDLL:
+    path = path or DEFAULT_LIB
+    if not os.path.exists(path):
+        raise AcossError("native library %s not found: build it with `python -m acoss_b200.build` "
+                         "(there is no CPU fallback)" % path)
+    lib = ctypes.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the ABI is incomplete
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+def pack_songs(songs):
+    """songs: list of dicts with 'chroma' (bins, L) [and 'gchroma' (bins,)] as Serra09.load_features
+    returns them (Serra09.py:154).  Returns (frames [total, bins], offsets i64, lengths i32,
+    gchroma f64 [n, bins] or None)."""
+    bins = songs[0]["chroma"].shape[0]
+    dt = np.float64 if any(s["chroma"].dtype == np.float64 for s in songs) else np.float32
+    lengths = np.array([s["chroma"].shape[1] for s in songs], dtype=np.int32)
+    offsets = np.zeros(len(songs), dtype=np.int64)
+    if len(songs) > 1:
+        offsets[1:] = np.cumsum(lengths[:-1].astype(np.int64))
+    total = int(lengths.sum())
+    frames = np.empty((max(total, 1), bins), dtype=dt)
+    for s, o, n in zip(songs, offsets, lengths):
+        frames[o:o + n] = s["chroma"].T
+    g = None
+    if all(("gchroma" in s and s["gchroma"] is not None) for s in songs):
+        g = np.ascontiguousarray(np.stack([np.asarray(s["gchroma"], dtype=np.float64) for s in songs]))
+    return frames, offsets, lengths, g
+
+
+class Context:
+    """One acoss_ctx (one GPU)."""
+
+    def __init__(self, device: int = 0, lib_path: str | None = None):
+        self.lib = load_library(lib_path)
+        self._h = ctypes.c_void_p()
+        self.lengths = None
+        self.bins = 0
+        rc = self.lib.acoss_create(ctypes.byref(self._h), int(device))
+        if rc != 0:
+            raise AcossError("acoss_create(%d) failed: %s" % (device, self._err()))
+
+    def _err(self):
+        e = self.lib.acoss_last_error()
+        return e.decode() if e else "?"
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise AcossError("%s failed (%d): %s" % (what, rc, self._err()))
+
+    def close(self):
+        if self._h:
+            self.lib.acoss_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ songs
+    def upload(self, frames, offsets, lengths, gchroma=None):
+        frames = np.ascontiguousarray(frames)
+        if frames.dtype == np.float32:
+            dt = F32
+        elif frames.dtype == np.float64:
+            dt = F64
+        else:
+            raise TypeError("frames must be float32 or float64, got %s" % frames.dtype)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+        if gchroma is not None:
+            gchroma = np.ascontiguousarray(gchroma, dtype=np.float64)
+        self.lengths = lengths.copy()
+        self.bins = int(frames.shape[1])
+        rc = self.lib.acoss_upload_songs(self._h, frames.ctypes.data_as(ctypes.c_void_p), dt,
+                                         _ptr(offsets, _c_i64p), _ptr(lengths, _c_i32p), len(lengths),
+                                         self.bins, _ptr(gchroma, _c_f64p))
+        self._check(rc, "acoss_upload_songs")
+
+    def upload_songs(self, songs):
+        self.upload(*pack_songs(songs))
+
+    # ------------------------------------------------------------------ scoring
+    def serra09_pairs(self, pairs, m=9, kappa=0.095, flags=0, want_crp=False, want_sw=False):
+        """pairs: (P, 2) int array.  Returns dict with qmax_raw, dmax_raw (float32), oti (int32),
+        shape (P, 2) = (M, N); with want_crp also 'crp' (list of uint8 (M, N) arrays in the
+        reference's orientation) -- a debug path."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        P = pairs.shape[0]
+        if want_sw:
+            flags |= FLAG_WANT_SW
+        q = np.zeros(P, np.float32)
+        d = np.zeros(P, np.float32)
+        sw = np.zeros(P, np.float32)
+        oti = np.zeros(P, np.int32)
+        shape = np.zeros((P, 2), np.int32)
+        crp_buf = crp_off = swapped = None
+        if want_crp:
+            L = self.lengths
+            Mi = np.maximum(L[pairs[:, 0]].astype(np.int64) - m + 1, 0)
+            Nj = np.maximum(L[pairs[:, 1]].astype(np.int64) - m + 1, 0)
+            # room for either orientation
+            words = np.maximum(Mi * ((Nj + 31) // 32), Nj * ((Mi + 31) // 32))
+            crp_off = np.zeros(P, np.int64)
+            if P > 1:
+                crp_off[1:] = np.cumsum(words[:-1])
+            crp_buf = np.zeros(max(int(words.sum()), 1), np.uint32)
+            swapped = np.zeros(P, np.int32)
+        rc = self.lib.acoss_serra09_pairs(self._h, _ptr(pairs, _c_i32p), P, int(m), float(kappa), int(flags),
+                                          _ptr(q, _c_f32p), _ptr(d, _c_f32p), _ptr(sw, _c_f32p), _ptr(oti, _c_i32p),
+                                          _ptr(shape, _c_i32p), _ptr(crp_buf, _c_u32p), _ptr(crp_off, _c_i64p),
+                                          _ptr(swapped, _c_i32p))
+        self._check(rc, "acoss_serra09_pairs")
+        out = {"qmax_raw": q, "dmax_raw": d, "oti": oti, "shape": shape}
+        if want_sw:
+            out["sw_raw"] = sw
+        if want_crp:
+            crps = []
+            for p in range(P):
+                M, N = int(shape[p, 0]), int(shape[p, 1])
+                if M <= 0 or N <= 0:
+                    crps.append(np.zeros((max(M, 0), max(N, 0)), np.uint8))
+                    continue
+                r, c = (N, M) if swapped[p] else (M, N)
+                wp = (c + 31) // 32
+                B = unpack_bits(crp_buf[crp_off[p]:crp_off[p] + r * wp].reshape(r, wp), c)
+                crps.append(np.ascontiguousarray(B.T) if swapped[p] else B)
+            out["crp"] = crps
+            out["swapped"] = swapped
+        return out
+
+    def align_dense(self, mats, kappa=0.095, flags=0, want_sw=False, want_crp=False):
+        """mats: list of 2-D float32/float64 dissimilarity matrices (EarlySNF.py:86).  Returns
+        (B, 3) float32 [qmax, dmax, sw] (+ list of uint8 CRPs with want_crp)."""
+        B = len(mats)
+        dt = np.float64 if any(a.dtype == np.float64 for a in mats) else np.float32
+        rows = np.array([a.shape[0] for a in mats], np.int32)
+        cols = np.array([a.shape[1] for a in mats], np.int32)
+        sizes = rows.astype(np.int64) * cols
+        offs = np.zeros(B, np.int64)
+        if B > 1:
+            offs[1:] = np.cumsum(sizes[:-1])
+        flat = np.empty(max(int(sizes.sum()), 1), dt)
+        for a, o, n in zip(mats, offs, sizes):
+            flat[o:o + n] = np.asarray(a, dtype=dt).reshape(-1)
+        if want_sw:
+            flags |= FLAG_WANT_SW
+        out = np.zeros((B, 3), np.float32)
+        crp_buf = crp_off = None
+        if want_crp:
+            words = rows.astype(np.int64) * ((cols + 31) // 32)
+            crp_off = np.zeros(B, np.int64)
+            if B > 1:
+                crp_off[1:] = np.cumsum(words[:-1])
+            crp_buf = np.zeros(max(int(words.sum()), 1), np.uint32)
+        rc = self.lib.acoss_align_dense(self._h, flat.ctypes.data_as(ctypes.c_void_p), F64 if dt == np.float64 else F32,
+                                        _ptr(offs, _c_i64p), _ptr(rows, _c_i32p), _ptr(cols, _c_i32p), B,
+                                        float(kappa), int(flags), _ptr(out, _c_f32p), _ptr(crp_buf, _c_u32p),
+                                        _ptr(crp_off, _c_i64p))
+        self._check(rc, "acoss_align_dense")
+        if want_crp:
+            crps = []
+            for b in range(B):
+                wp = (int(cols[b]) + 31) // 32
+                crps.append(unpack_bits(crp_buf[crp_off[b]:crp_off[b] + int(rows[b]) * wp].reshape(int(rows[b]), wp),
+                                        int(cols[b])))
+            return out, crps
+        return out
+
+    def dp_packed(self, plots, flags=0, want_sw=False):
+        """plots: list of uint8 (rows, cols) binary matrices.  Returns (B, 3) [qmax, dmax, sw]."""
+        B = len(plots)
+        rows = np.array([a.shape[0] for a in plots], np.int32)
+        cols = np.array([a.shape[1] for a in plots], np.int32)
+        packed = [pack_bits(np.asarray(a, dtype=np.uint8)) for a in plots]
+        words = np.array([p.size for p in packed], np.int64)
+        offs = np.zeros(B, np.int64)
+        if B > 1:
+            offs[1:] = np.cumsum(words[:-1])
+        buf = np.zeros(max(int(words.sum()), 1), np.uint32)
+        for p, o in zip(packed, offs):
+            buf[o:o + p.size] = p.reshape(-1)
+        if want_sw:
+            flags |= FLAG_WANT_SW
+        out = np.zeros((B, 3), np.float32)
+        rc = self.lib.acoss_dp_packed(self._h, _ptr(buf, _c_u32p), _ptr(offs, _c_i64p), _ptr(rows, _c_i32p),
+                                      _ptr(cols, _c_i32p), B, int(flags), _ptr(out, _c_f32p))
+        self._check(rc, "acoss_dp_packed")
+        return out
+
+    # pySeqAlign-compatible scalar calls (pySeqAlign.pyx:7-23)
+    def _scalar(self, fn, S, a, b):
+        S = np.ascontiguousarray(S, dtype=np.uint8).reshape(-1)
+        if S.size < a * b:
+            raise ValueError("S has %d elements, need %d" % (S.size, a * b))
+        r = ctypes.c_float(0.0)
+        self._check(fn(self._h, _ptr(S, _c_u8p), int(a), int(b), ctypes.byref(r)), fn.__name__)
+        return float(r.value)
+
+    def qmax(self, S, M, N):
+        return self._scalar(self.lib.acoss_qmax, S, M, N)
+
+    def dmax(self, S, M, N):
+        return self._scalar(self.lib.acoss_dmax, S, M, N)
+
+    def swconstrained(self, S, N, M):
+        return self._scalar(self.lib.acoss_swconstrained, S, N, M)
+
+    def qmax_dmax(self, S, M, N):
+        S = np.ascontiguousarray(S, dtype=np.uint8).reshape(-1)
+        q, d = ctypes.c_float(0.0), ctypes.c_float(0.0)
+        self._check(self.lib.acoss_qmax_dmax(self._h, _ptr(S, _c_u8p), int(M), int(N), ctypes.byref(q), ctypes.byref(d)),
+                    "acoss_qmax_dmax")
+        return float(q.value), float(d.value)
+
+    # ------------------------------------------------------------------ accounting
+    def kernel_launches(self):
+        return int(self.lib.acoss_kernel_launches(self._h))
+
+    def reset_counters(self):
+        self.lib.acoss_reset_counters(self._h)
+
+    def last_stage_ms(self):
+        out = np.zeros(5, np.float32)
+        self._check(self.lib.acoss_last_stage_ms(self._h, _ptr(out, _c_f32p)), "acoss_last_stage_ms")
+        return dict(zip(["oti", "thresholds", "crp", "dp", "total"], out.tolist()))
+
+
+def pack_bits(B):
+    """(rows, cols) 0/1 -> (rows, ceil(cols/32)) uint32, bit t of word w = B[:, 32w+t]."""
+    B = np.asarray(B, dtype=np.uint8)
+    rows, cols = B.shape
+    wp = (cols + 31) // 32
+    pad = np.zeros((rows, wp * 32), dtype=np.uint8)
+    pad[:, :cols] = B != 0
+    by = np.packbits(pad.reshape(rows, wp, 4, 8), axis=-1, bitorder="little").reshape(rows, wp, 4)
+    return np.ascontiguousarray(by).view(np.uint32).reshape(rows, wp) if by.size else np.zeros((rows, wp), np.uint32)
+
+
+def unpack_bits(P, cols):
+    P = np.ascontiguousarray(P, dtype=np.uint32)
+    rows, wp = P.shape
+    by = P.view(np.uint8).reshape(rows, wp * 4)
+    bits = np.unpackbits(by, axis=1, bitorder="little")
+    return np.ascontiguousarray(bits[:, :cols])

@@ -1,0 +1,779 @@
+// api.cu -- host side of libacoss_b200.so: the C ABI declared in include/acoss_b200.h.
+// Owns device memory and the stream, cuts the pair list into chunks whose scratch
+// (separators, packed CRPs) fits a fixed budget, and launches the kernels:
+//   k_oti -> k_sweep<MODE 0> (both orientations) -> k_sweep<MODE 1> -> k_dp.
+// There is no CPU path: every entry point fails with ACOSS_ERR_CUDA when the device is
+// missing or a launch fails.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "../../include/acoss_b200.h"
+#include "common.cuh"
+#include "kernels_dense.cuh"
+#include "kernels_dp.cuh"
+#include "kernels_prep.cuh"
+#include "kernels_sweep.cuh"
+
+#ifdef ACOSS_EMU
+#define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
+    emu::launch(dim3((unsigned)(grid)), dim3((unsigned)(block)), (size_t)(smem), [&]() { kfn(__VA_ARGS__); })
+template <class F>
+static cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, F, int, size_t) {
+    *n = 1;
+    return cudaSuccess;
+}
+#else
+#define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) kfn<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#endif
+
+using namespace acoss;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(ACOSS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+int neighbours(double kappa, int n) {
+    // CRPUtils.py:188-193: int(np.round(kappa*n)) (round-half-even on the double product)
+    if (kappa < 1.0) return (int)std::nearbyint(kappa * (double)n);
+    return (int)kappa;
+}
+
+}  // namespace
+
+struct acoss_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int sm_count = 0;
+    int max_smem = 0;
+    // songs
+    DevBuf frames, norms, offs, gchroma;
+    std::vector<int64_t> h_offs;
+    std::vector<int32_t> h_len;
+    int n_songs = 0, bins = 0;
+    int64_t total_frames = 0;
+    bool has_gchroma = false;
+    // per-chunk scratch
+    DevBuf pairs, items, counters, seps, crp, bnd, qout, dout, swout, otiout, gscratch;
+    DevBuf dense_in, dense_desc, dense_starts;
+    PinBuf h_stage;
+    std::vector<uint32_t> h_crp;
+    // accounting
+    int64_t launches = 0;
+    float stage_ms[5] = {0, 0, 0, 0, 0};
+    bool have_stage_ms = false;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+
+namespace {
+
+constexpr int kMaxChunkPairs = 1 << 18;
+constexpr int64_t kMaxChunkSepDoubles = (int64_t)1 << 28;  // 2 GiB
+constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
+constexpr int kCounterSlots = 16;
+
+struct ItemLists {
+    std::vector<uint32_t> thrA, thrB, crpA, crpB, dp4, dp8, dp16;
+    int thrB_w = 0, crpB_w = 0;
+};
+
+template <int BINS, int THREADS, int MODE>
+int launch_sweep(acoss_ctx* c, const uint32_t* d_items, int n_items, int Wmax, int m, unsigned int* d_counter,
+                 uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    auto kfn = k_sweep<BINS, THREADS, MODE>;
+    const int R = 8;
+    const int RD = m + 1;
+    const size_t fixed = sweep_smem_fixed_bytes(Wmax, BINS);
+    const size_t var = (size_t)(RD + (MODE == 0 ? R : 0)) * Wmax * sizeof(double);
+    const size_t budget = (size_t)c->max_smem - 1024;  // static shared + launch reserve
+    const bool use_g = fixed + var > budget;
+    const size_t smem = use_g ? fixed : fixed + var;
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, THREADS, smem));
+    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep cannot be resident (smem %zu B)", smem);
+    const int grid = std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
+    SweepArgs A;
+    A.frames = c->frames.as<double>();
+    A.norms = c->norms.as<double>();
+    A.offs = c->offs.as<int64_t>();
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.counter = d_counter;
+    A.seps = c->seps.as<double>();
+    A.crp = c->crp.as<uint32_t>();
+    A.m = m;
+    A.R = R;
+    A.Wmax = Wmax;
+    A.use_gscratch = use_g ? 1 : 0;
+    A.gscratch = nullptr;
+    A.gscratch_stride = 0;
+    A.flags = flags;
+    if (use_g) {
+        A.gscratch_stride = (int64_t)(RD + R) * Wmax;
+        CU(c->gscratch.reserve((size_t)grid * A.gscratch_stride * sizeof(double)));
+        A.gscratch = c->gscratch.as<double>();
+    }
+    ACOSS_LAUNCH(kfn, grid, THREADS, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
+template <int CPL>
+int launch_dp(acoss_ctx* c, const uint32_t* d_items, int n_items, uint32_t flags, float* q, float* d, float* sw) {
+    if (n_items <= 0) return ACOSS_OK;
+    DpArgs A;
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.crp = c->crp.as<uint32_t>();
+    A.bnd = c->bnd.as<int4>();
+    A.qmax_out = q;
+    A.dmax_out = d;
+    A.sw_out = sw;
+    A.flags = flags;
+    const int grid = (n_items + 3) / 4;
+    if (flags & kFlagWantSw) {
+        auto kfn = k_dp<CPL, true>;
+        ACOSS_LAUNCH(kfn, grid, 128, 0, c->stream, A);
+    } else {
+        auto kfn = k_dp<CPL, false>;
+        ACOSS_LAUNCH(kfn, grid, 128, 0, c->stream, A);
+    }
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
+// Upload item lists, run the DP kernels over the PairWork records already on the device.
+int run_dp_lists(acoss_ctx* c, const ItemLists& L, const uint32_t* d_items_base, size_t off4, size_t off8,
+                 size_t off16, uint32_t flags) {
+    float* q = c->qout.as<float>();
+    float* d = c->dout.as<float>();
+    float* sw = c->swout.as<float>();
+    int rc;
+    if ((rc = launch_dp<4>(c, d_items_base + off4, (int)L.dp4.size(), flags, q, d, sw)) != ACOSS_OK) return rc;
+    if ((rc = launch_dp<8>(c, d_items_base + off8, (int)L.dp8.size(), flags, q, d, sw)) != ACOSS_OK) return rc;
+    if ((rc = launch_dp<16>(c, d_items_base + off16, (int)L.dp16.size(), flags, q, d, sw)) != ACOSS_OK) return rc;
+    return ACOSS_OK;
+}
+
+void classify_dp(ItemLists& L, uint32_t p, int cols) {
+    if (cols <= 128)
+        L.dp4.push_back(p);
+    else if (cols <= 256)
+        L.dp8.push_back(p);
+    else
+        L.dp16.push_back(p);
+}
+
+int64_t bnd_records(int rows, int cols) {
+    // wide plots (more than one 512-column block in the CPL=16 kernel) need the hand-over scratch
+    return cols > 512 ? (int64_t)rows * 2 * 2 : 0;
+}
+
+template <int BINS>
+int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, double kappa, uint32_t flags,
+              float* qmax_raw, float* dmax_raw, float* sw_raw, int32_t* oti_out, int32_t* shape_out,
+              uint32_t* crp_out, const int64_t* crp_offsets, int32_t* crp_swapped_out) {
+    // ---- host: work records + item lists
+    std::vector<PairWork> W((size_t)n);
+    ItemLists L;
+    int64_t sep_total = 0, crp_total = 0, bnd_total = 0;
+    const bool noswap = (flags & kFlagNoSwap) != 0;
+    const bool nonmutual = (flags & kFlagNonMutual) != 0;
+    for (int p = 0; p < n; ++p) {
+        PairWork& w = W[p];
+        w.song_i = pairs[2 * (p0 + p)];
+        w.song_j = pairs[2 * (p0 + p) + 1];
+        w.Li = c->h_len[w.song_i];
+        w.Lj = c->h_len[w.song_j];
+        w.M = w.Li - m + 1;
+        w.N = w.Lj - m + 1;
+        const bool ok = w.M > 0 && w.N > 0;
+        w.k_row = ok ? neighbours(kappa, w.N) : 0;
+        w.k_col = ok ? neighbours(kappa, w.M) : 0;
+        w.oti = 0;
+        w.swap = (!noswap && w.Lj > w.Li) ? 1 : 0;
+        w.crp_rows = ok ? (w.swap ? w.N : w.M) : 0;
+        w.crp_cols = ok ? (w.swap ? w.M : w.N) : 0;
+        w.crp_wp = (w.crp_cols + 31) / 32;
+        w.pad0 = 0;
+        w.sep_off = sep_total;
+        w.crp_off = crp_total;
+        const int64_t br = bnd_records(w.crp_rows, w.crp_cols);
+        w.bnd_off = br > 0 ? bnd_total : -1;
+        bnd_total += br;
+        if (ok) {
+            sep_total += (int64_t)w.M + w.N;
+            crp_total += (int64_t)w.crp_rows * w.crp_wp;
+            // threshold sweeps: orientation 0 has song j on the columns, orientation 1 song i
+            const int wA = 128 * kSweepCPL, wB = 256 * kSweepCPL;
+            for (int o = 0; o < 2; ++o) {
+                if (o == 1 && nonmutual) break;
+                const int Lc = o ? w.Li : w.Lj;
+                if (Lc <= wA) {
+                    L.thrA.push_back((uint32_t)p * 2 + o);
+                } else {
+                    L.thrB.push_back((uint32_t)p * 2 + o);
+                    L.thrB_w = std::max(L.thrB_w, (Lc + wB - 1) / wB * wB);
+                }
+            }
+            const int Lc = w.swap ? w.Li : w.Lj;
+            if (Lc <= wA) {
+                L.crpA.push_back((uint32_t)p);
+            } else {
+                L.crpB.push_back((uint32_t)p);
+                L.crpB_w = std::max(L.crpB_w, (Lc + wB - 1) / wB * wB);
+            }
+        }
+        classify_dp(L, (uint32_t)p, w.crp_cols);
+    }
+    // ---- device buffers
+    CU(c->pairs.reserve((size_t)n * sizeof(PairWork)));
+    CU(c->seps.reserve((size_t)std::max<int64_t>(sep_total, 1) * sizeof(double)));
+    CU(c->crp.reserve((size_t)std::max<int64_t>(crp_total, 1) * sizeof(uint32_t)));
+    CU(c->bnd.reserve((size_t)std::max<int64_t>(bnd_total, 1) * sizeof(int4)));
+    CU(c->qout.reserve((size_t)n * sizeof(float)));
+    CU(c->dout.reserve((size_t)n * sizeof(float)));
+    CU(c->swout.reserve((size_t)n * sizeof(float)));
+    CU(c->otiout.reserve((size_t)n * sizeof(int32_t)));
+    CU(c->counters.reserve(kCounterSlots * sizeof(unsigned int)));
+    const size_t n_items = L.thrA.size() + L.thrB.size() + L.crpA.size() + L.crpB.size() + L.dp4.size() +
+                           L.dp8.size() + L.dp16.size();
+    CU(c->items.reserve(std::max<size_t>(n_items, 1) * sizeof(uint32_t)));
+    // stage: [PairWork...][items...]
+    const size_t pw_bytes = (size_t)n * sizeof(PairWork);
+    CU(c->h_stage.reserve(pw_bytes + n_items * sizeof(uint32_t) + 64));
+    memcpy(c->h_stage.p, W.data(), pw_bytes);
+    uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_stage.as<char>() + pw_bytes);
+    size_t o_thrA = 0, o_thrB, o_crpA, o_crpB, o_dp4, o_dp8, o_dp16, pos = 0;
+    auto put = [&](const std::vector<uint32_t>& v) {
+        size_t at = pos;
+        if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
+        pos += v.size();
+        return at;
+    };
+    o_thrA = put(L.thrA);
+    o_thrB = put(L.thrB);
+    o_crpA = put(L.crpA);
+    o_crpB = put(L.crpB);
+    o_dp4 = put(L.dp4);
+    o_dp8 = put(L.dp8);
+    o_dp16 = put(L.dp16);
+    CU(cudaMemcpyAsync(c->pairs.p, c->h_stage.p, pw_bytes, cudaMemcpyHostToDevice, c->stream));
+    if (n_items)
+        CU(cudaMemcpyAsync(c->items.p, hi, n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemsetAsync(c->counters.p, 0, kCounterSlots * sizeof(unsigned int), c->stream));
+    const uint32_t* d_items = c->items.as<uint32_t>();
+    unsigned int* d_cnt = c->counters.as<unsigned int>();
+
+    // ---- kernels
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    {
+        auto kfn = k_oti;
+        const int no_oti = ((flags & kFlagNoOti) || !c->has_gchroma) ? 1 : 0;
+        ACOSS_LAUNCH(kfn, (n + 127) / 128, 128, 0, c->stream, c->pairs.as<PairWork>(), n,
+                     c->gchroma.as<double>(), c->bins, no_oti);
+        c->launches++;
+        CU(cudaGetLastError());
+    }
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    int rc;
+    const int wA = 128 * kSweepCPL;
+    if ((rc = launch_sweep<BINS, 128, 0>(c, d_items + o_thrA, (int)L.thrA.size(), wA, m, d_cnt + 0, flags))) return rc;
+    if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_thrB, (int)L.thrB.size(), L.thrB_w, m, d_cnt + 1, flags))) return rc;
+    CU(cudaEventRecord(c->ev[2], c->stream));
+    if ((rc = launch_sweep<BINS, 128, 1>(c, d_items + o_crpA, (int)L.crpA.size(), wA, m, d_cnt + 2, flags))) return rc;
+    if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_crpB, (int)L.crpB.size(), L.crpB_w, m, d_cnt + 3, flags))) return rc;
+    CU(cudaEventRecord(c->ev[3], c->stream));
+    if ((rc = run_dp_lists(c, L, d_items, o_dp4, o_dp8, o_dp16, flags))) return rc;
+    CU(cudaEventRecord(c->ev[4], c->stream));
+
+    // ---- results
+    if (qmax_raw) CU(cudaMemcpyAsync(qmax_raw + p0, c->qout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    if (dmax_raw) CU(cudaMemcpyAsync(dmax_raw + p0, c->dout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    if (sw_raw && (flags & kFlagWantSw))
+        CU(cudaMemcpyAsync(sw_raw + p0, c->swout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    if (oti_out || crp_swapped_out) {
+        // the oti lives in the PairWork records
+        CU(cudaMemcpyAsync(c->h_stage.p, c->pairs.p, pw_bytes, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (crp_out) {
+        c->h_crp.resize((size_t)std::max<int64_t>(crp_total, 1));
+        CU(cudaMemcpyAsync(c->h_crp.data(), c->crp.p, (size_t)crp_total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    for (int s = 0; s < 4; ++s) {
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c->ev[s], c->ev[s + 1]));
+        c->stage_ms[s] += ms;
+    }
+    {
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c->ev[0], c->ev[4]));
+        c->stage_ms[4] += ms;
+    }
+    const PairWork* back = c->h_stage.as<PairWork>();
+    for (int p = 0; p < n; ++p) {
+        if (oti_out) oti_out[p0 + p] = back[p].oti;
+        if (crp_swapped_out) crp_swapped_out[p0 + p] = W[p].swap;
+        if (shape_out) {
+            shape_out[2 * (p0 + p)] = W[p].M;
+            shape_out[2 * (p0 + p) + 1] = W[p].N;
+        }
+        if (sw_raw && !(flags & kFlagWantSw)) sw_raw[p0 + p] = 0.0f;
+        if (crp_out && crp_offsets) {
+            const size_t words = (size_t)W[p].crp_rows * W[p].crp_wp;
+            if (words) memcpy(crp_out + crp_offsets[p0 + p], c->h_crp.data() + W[p].crp_off, words * sizeof(uint32_t));
+        }
+    }
+    return ACOSS_OK;
+}
+
+int check_ctx(acoss_ctx* c) {
+    if (!c) return fail(ACOSS_ERR_ARG, "null context");
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(ACOSS_ERR_CUDA, "cudaSetDevice(%d): %s", c->device, cudaGetErrorString(e));
+    return ACOSS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* acoss_last_error(void) { return g_last_error.c_str(); }
+int acoss_version(void) { return 100; }
+
+int acoss_create(acoss_ctx** out, int device) {
+    if (!out) return fail(ACOSS_ERR_ARG, "out is null");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0)
+        return fail(ACOSS_ERR_CUDA, "no CUDA device available (%s); this library has no CPU path",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    if (device < 0 || device >= ndev) return fail(ACOSS_ERR_ARG, "device %d out of range (0..%d)", device, ndev - 1);
+    CU(cudaSetDevice(device));
+    acoss_ctx* c = new acoss_ctx();
+    c->device = device;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    CU(cudaDeviceGetAttribute(&c->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    for (int i = 0; i < 5; ++i) CU(cudaEventCreate(&c->ev[i]));
+    *out = c;
+    return ACOSS_OK;
+}
+
+int acoss_destroy(acoss_ctx* c) {
+    if (!c) return ACOSS_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->frames, &c->norms, &c->offs, &c->gchroma, &c->pairs, &c->items, &c->counters,
+                      &c->seps, &c->crp, &c->bnd, &c->qout, &c->dout, &c->swout, &c->otiout, &c->gscratch,
+                      &c->dense_in, &c->dense_desc, &c->dense_starts};
+    for (DevBuf* b : bufs) b->release();
+    c->h_stage.release();
+    for (int i = 0; i < 5; ++i)
+        if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return ACOSS_OK;
+}
+
+int acoss_upload_songs(acoss_ctx* c, const void* frames, int dtype, const int64_t* offsets, const int32_t* lengths,
+                       int32_t n_songs, int32_t bins, const double* gchroma) {
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!frames || !offsets || !lengths) return fail(ACOSS_ERR_ARG, "null input");
+    if (n_songs <= 0) return fail(ACOSS_ERR_ARG, "n_songs must be positive");
+    if (bins != 12 && bins != 13) return fail(ACOSS_ERR_ARG, "bins must be 12 (chroma) or 13 (mfcc), got %d", bins);
+    if (dtype != ACOSS_F32 && dtype != ACOSS_F64) return fail(ACOSS_ERR_ARG, "unknown dtype %d", dtype);
+    int64_t total = 0;
+    for (int s = 0; s < n_songs; ++s) {
+        if (lengths[s] < 0 || offsets[s] < 0) return fail(ACOSS_ERR_ARG, "negative length/offset for song %d", s);
+        total = std::max<int64_t>(total, offsets[s] + lengths[s]);
+    }
+    c->n_songs = n_songs;
+    c->bins = bins;
+    c->total_frames = total;
+    c->h_offs.assign(offsets, offsets + n_songs);
+    c->h_len.assign(lengths, lengths + n_songs);
+    const size_t n_el = (size_t)total * bins;
+    CU(c->frames.reserve(std::max<size_t>(n_el, 1) * sizeof(double)));
+    CU(c->norms.reserve(std::max<size_t>((size_t)total, 1) * sizeof(double)));
+    CU(c->offs.reserve((size_t)n_songs * sizeof(int64_t)));
+    if (dtype == ACOSS_F64) {
+        CU(cudaMemcpyAsync(c->frames.p, frames, n_el * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    } else {
+        CU(c->dense_in.reserve(std::max<size_t>(n_el, 1) * sizeof(float)));
+        CU(cudaMemcpyAsync(c->dense_in.p, frames, n_el * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+        if (n_el) {
+            auto kfn = k_f32_to_f64;
+            ACOSS_LAUNCH(kfn, (n_el + 255) / 256, 256, 0, c->stream, c->dense_in.as<float>(), c->frames.as<double>(),
+                         (int64_t)n_el);
+            c->launches++;
+        }
+    }
+    CU(cudaMemcpyAsync(c->offs.p, offsets, (size_t)n_songs * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+    if (total) {
+        auto kfn = k_norms<double>;
+        ACOSS_LAUNCH(kfn, (total + 255) / 256, 256, 0, c->stream, c->frames.as<double>(), c->norms.as<double>(), total,
+                     (int)bins);
+        c->launches++;
+    }
+    c->has_gchroma = gchroma != nullptr;
+    CU(c->gchroma.reserve((size_t)n_songs * bins * sizeof(double)));
+    if (gchroma)
+        CU(cudaMemcpyAsync(c->gchroma.p, gchroma, (size_t)n_songs * bins * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
+int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m, double kappa, uint32_t flags,
+                        float* qmax_raw, float* dmax_raw, float* sw_raw, int32_t* oti_out, int32_t* shape_out,
+                        uint32_t* crp_out, const int64_t* crp_offsets, int32_t* crp_swapped_out) {
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (c->n_songs <= 0) return fail(ACOSS_ERR_STATE, "acoss_upload_songs has not been called");
+    if (P < 0 || (P > 0 && !pairs)) return fail(ACOSS_ERR_ARG, "bad pair list");
+    if (m < 1) return fail(ACOSS_ERR_ARG, "m must be >= 1");
+    if (!(kappa > 0.0)) return fail(ACOSS_ERR_ARG, "kappa must be > 0");
+    if (crp_out && !crp_offsets) return fail(ACOSS_ERR_ARG, "crp_out needs crp_offsets");
+    if (!(flags & kFlagNoOti) && !c->has_gchroma) return fail(ACOSS_ERR_STATE, "OTI requested but no gchroma uploaded");
+    for (int64_t p = 0; p < P; ++p) {
+        const int32_t i = pairs[2 * p], j = pairs[2 * p + 1];
+        if (i < 0 || i >= c->n_songs || j < 0 || j >= c->n_songs)
+            return fail(ACOSS_ERR_ARG, "pair %lld = (%d, %d) out of range (n_songs %d)", (long long)p, i, j, c->n_songs);
+    }
+    for (int s = 0; s < 5; ++s) c->stage_ms[s] = 0.f;
+    c->have_stage_ms = true;
+    int64_t p0 = 0;
+    while (p0 < P) {
+        // cut a chunk whose scratch fits the budget
+        int n = 0;
+        int64_t sep = 0, crp = 0;
+        while (p0 + n < P && n < kMaxChunkPairs) {
+            const int Li = c->h_len[pairs[2 * (p0 + n)]], Lj = c->h_len[pairs[2 * (p0 + n) + 1]];
+            const int64_t M = std::max(Li - m + 1, 0), N = std::max(Lj - m + 1, 0);
+            const int64_t s2 = M + N, c2 = std::max(M, N) * ((std::min(M, N) + 31) / 32 + 1);
+            if (n > 0 && (sep + s2 > kMaxChunkSepDoubles || crp + c2 > kMaxChunkCrpWords)) break;
+            sep += s2;
+            crp += c2;
+            ++n;
+        }
+        if (c->bins == 12)
+            rc = run_chunk<12>(c, pairs, p0, n, m, kappa, flags, qmax_raw, dmax_raw, sw_raw, oti_out, shape_out,
+                               crp_out, crp_offsets, crp_swapped_out);
+        else
+            rc = run_chunk<13>(c, pairs, p0, n, m, kappa, flags, qmax_raw, dmax_raw, sw_raw, oti_out, shape_out,
+                               crp_out, crp_offsets, crp_swapped_out);
+        if (rc) return rc;
+        p0 += n;
+    }
+    return ACOSS_OK;
+}
+
+int acoss_dp_packed(acoss_ctx* c, const uint32_t* crp, const int64_t* crp_offsets, const int32_t* rows,
+                    const int32_t* cols, int32_t B, uint32_t flags, float* out) {
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (B < 0 || (B > 0 && (!crp || !crp_offsets || !rows || !cols || !out))) return fail(ACOSS_ERR_ARG, "null input");
+    if (B == 0) return ACOSS_OK;
+    std::vector<PairWork> W((size_t)B);
+    ItemLists L;
+    int64_t crp_total = 0, bnd_total = 0;
+    for (int b = 0; b < B; ++b) {
+        if (rows[b] < 0 || cols[b] < 0) return fail(ACOSS_ERR_ARG, "negative shape for plot %d", b);
+        PairWork& w = W[b];
+        memset(&w, 0, sizeof(w));
+        w.crp_rows = rows[b];
+        w.crp_cols = cols[b];
+        w.crp_wp = (cols[b] + 31) / 32;
+        w.crp_off = crp_total;
+        crp_total += (int64_t)w.crp_rows * w.crp_wp;
+        const int64_t br = bnd_records(w.crp_rows, w.crp_cols);
+        w.bnd_off = br > 0 ? bnd_total : -1;
+        bnd_total += br;
+        classify_dp(L, (uint32_t)b, w.crp_cols);
+    }
+    CU(c->pairs.reserve((size_t)B * sizeof(PairWork)));
+    CU(c->crp.reserve((size_t)std::max<int64_t>(crp_total, 1) * sizeof(uint32_t)));
+    CU(c->bnd.reserve((size_t)std::max<int64_t>(bnd_total, 1) * sizeof(int4)));
+    CU(c->qout.reserve((size_t)B * sizeof(float)));
+    CU(c->dout.reserve((size_t)B * sizeof(float)));
+    CU(c->swout.reserve((size_t)B * sizeof(float)));
+    CU(c->items.reserve((size_t)B * sizeof(uint32_t)));
+    // gather the plots into the device arena
+    c->h_crp.resize((size_t)std::max<int64_t>(crp_total, 1));
+    for (int b = 0; b < B; ++b) {
+        const size_t words = (size_t)W[b].crp_rows * W[b].crp_wp;
+        if (words) memcpy(c->h_crp.data() + W[b].crp_off, crp + crp_offsets[b], words * sizeof(uint32_t));
+    }
+    std::vector<uint32_t> items;
+    items.insert(items.end(), L.dp4.begin(), L.dp4.end());
+    items.insert(items.end(), L.dp8.begin(), L.dp8.end());
+    items.insert(items.end(), L.dp16.begin(), L.dp16.end());
+    CU(cudaMemcpyAsync(c->pairs.p, W.data(), (size_t)B * sizeof(PairWork), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->crp.p, c->h_crp.data(), (size_t)crp_total * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->items.p, items.data(), items.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemsetAsync(c->swout.p, 0, (size_t)B * sizeof(float), c->stream));
+    rc = run_dp_lists(c, L, c->items.as<uint32_t>(), 0, L.dp4.size(), L.dp4.size() + L.dp8.size(), flags);
+    if (rc) return rc;
+    std::vector<float> q((size_t)B), d((size_t)B), s((size_t)B);
+    CU(cudaMemcpyAsync(q.data(), c->qout.p, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(d.data(), c->dout.p, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(s.data(), c->swout.p, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    for (int b = 0; b < B; ++b) {
+        out[3 * b] = q[b];
+        out[3 * b + 1] = d[b];
+        out[3 * b + 2] = (flags & kFlagWantSw) ? s[b] : 0.0f;
+    }
+    return ACOSS_OK;
+}
+
+int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* csm_offsets, const int32_t* rows,
+                      const int32_t* cols, int32_t B, double kappa, uint32_t flags, float* out, uint32_t* crp_out,
+                      const int64_t* crp_offsets) {
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (B < 0 || (B > 0 && (!csm || !csm_offsets || !rows || !cols || !out))) return fail(ACOSS_ERR_ARG, "null input");
+    if (dtype != ACOSS_F32 && dtype != ACOSS_F64) return fail(ACOSS_ERR_ARG, "unknown dtype %d", dtype);
+    if (!(kappa > 0.0)) return fail(ACOSS_ERR_ARG, "kappa must be > 0");
+    if (crp_out && !crp_offsets) return fail(ACOSS_ERR_ARG, "crp_out needs crp_offsets");
+    if (B == 0) return ACOSS_OK;
+    const size_t esz = dtype == ACOSS_F64 ? sizeof(double) : sizeof(float);
+    std::vector<PairWork> W((size_t)B);
+    std::vector<DenseDesc> D((size_t)B);
+    std::vector<int64_t> starts((size_t)2 * B);  // [line_start | word_start]
+    ItemLists L;
+    int64_t el_total = 0, sep_total = 0, crp_total = 0, bnd_total = 0, lines = 0;
+    for (int b = 0; b < B; ++b) {
+        if (rows[b] <= 0 || cols[b] <= 0) return fail(ACOSS_ERR_ARG, "empty matrix %d", b);
+        DenseDesc& d = D[b];
+        d.rows = rows[b];
+        d.cols = cols[b];
+        d.k_row = neighbours(kappa, cols[b]);
+        d.k_col = neighbours(kappa, rows[b]);
+        d.wp = (cols[b] + 31) / 32;
+        d.pad = 0;
+        d.csm_off = el_total;
+        d.sep_off = sep_total;
+        d.crp_off = crp_total;
+        starts[b] = lines;
+        starts[B + b] = crp_total;
+        PairWork& w = W[b];
+        memset(&w, 0, sizeof(w));
+        w.crp_rows = d.rows;
+        w.crp_cols = d.cols;
+        w.crp_wp = d.wp;
+        w.crp_off = crp_total;
+        const int64_t br = bnd_records(w.crp_rows, w.crp_cols);
+        w.bnd_off = br > 0 ? bnd_total : -1;
+        bnd_total += br;
+        classify_dp(L, (uint32_t)b, w.crp_cols);
+        el_total += (int64_t)d.rows * d.cols;
+        sep_total += (int64_t)d.rows + d.cols;
+        crp_total += (int64_t)d.rows * d.wp;
+        lines += (int64_t)d.rows + d.cols;
+    }
+    CU(c->dense_in.reserve((size_t)el_total * esz));
+    CU(c->dense_desc.reserve((size_t)B * sizeof(DenseDesc)));
+    CU(c->dense_starts.reserve((size_t)2 * B * sizeof(int64_t)));
+    CU(c->pairs.reserve((size_t)B * sizeof(PairWork)));
+    CU(c->seps.reserve((size_t)sep_total * sizeof(double)));
+    CU(c->crp.reserve((size_t)crp_total * sizeof(uint32_t)));
+    CU(c->bnd.reserve((size_t)std::max<int64_t>(bnd_total, 1) * sizeof(int4)));
+    CU(c->qout.reserve((size_t)B * sizeof(float)));
+    CU(c->dout.reserve((size_t)B * sizeof(float)));
+    CU(c->swout.reserve((size_t)B * sizeof(float)));
+    CU(c->items.reserve((size_t)B * sizeof(uint32_t)));
+    for (int b = 0; b < B; ++b)
+        CU(cudaMemcpyAsync(c->dense_in.as<char>() + D[b].csm_off * esz,
+                           reinterpret_cast<const char*>(csm) + csm_offsets[b] * esz,
+                           (size_t)D[b].rows * D[b].cols * esz, cudaMemcpyHostToDevice, c->stream));
+    std::vector<uint32_t> items;
+    items.insert(items.end(), L.dp4.begin(), L.dp4.end());
+    items.insert(items.end(), L.dp8.begin(), L.dp8.end());
+    items.insert(items.end(), L.dp16.begin(), L.dp16.end());
+    CU(cudaMemcpyAsync(c->dense_desc.p, D.data(), (size_t)B * sizeof(DenseDesc), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->dense_starts.p, starts.data(), (size_t)2 * B * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->pairs.p, W.data(), (size_t)B * sizeof(PairWork), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->items.p, items.data(), items.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemsetAsync(c->swout.p, 0, (size_t)B * sizeof(float), c->stream));
+    const int mutual = (flags & kFlagNonMutual) ? 0 : 1;
+    const int64_t* d_line_start = c->dense_starts.as<int64_t>();
+    const int64_t* d_word_start = d_line_start + B;
+    if (dtype == ACOSS_F64) {
+        auto k1 = k_dense_seps<double>;
+        ACOSS_LAUNCH(k1, (lines + 3) / 4, 128, 0, c->stream, c->dense_in.as<double>(), c->dense_desc.as<DenseDesc>(),
+                     d_line_start, (int)B, lines, c->seps.as<double>());
+        auto k2 = k_dense_bits<double>;
+        ACOSS_LAUNCH(k2, (crp_total + 255) / 256, 256, 0, c->stream, c->dense_in.as<double>(),
+                     c->dense_desc.as<DenseDesc>(), d_word_start, (int)B, crp_total, c->seps.as<double>(),
+                     c->crp.as<uint32_t>(), mutual);
+    } else {
+        auto k1 = k_dense_seps<float>;
+        ACOSS_LAUNCH(k1, (lines + 3) / 4, 128, 0, c->stream, c->dense_in.as<float>(), c->dense_desc.as<DenseDesc>(),
+                     d_line_start, (int)B, lines, c->seps.as<double>());
+        auto k2 = k_dense_bits<float>;
+        ACOSS_LAUNCH(k2, (crp_total + 255) / 256, 256, 0, c->stream, c->dense_in.as<float>(),
+                     c->dense_desc.as<DenseDesc>(), d_word_start, (int)B, crp_total, c->seps.as<double>(),
+                     c->crp.as<uint32_t>(), mutual);
+    }
+    c->launches += 2;
+    CU(cudaGetLastError());
+    rc = run_dp_lists(c, L, c->items.as<uint32_t>(), 0, L.dp4.size(), L.dp4.size() + L.dp8.size(), flags);
+    if (rc) return rc;
+    std::vector<float> q((size_t)B), d((size_t)B), s((size_t)B);
+    CU(cudaMemcpyAsync(q.data(), c->qout.p, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(d.data(), c->dout.p, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(s.data(), c->swout.p, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    if (crp_out) {
+        c->h_crp.resize((size_t)crp_total);
+        CU(cudaMemcpyAsync(c->h_crp.data(), c->crp.p, (size_t)crp_total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    for (int b = 0; b < B; ++b) {
+        out[3 * b] = q[b];
+        out[3 * b + 1] = d[b];
+        out[3 * b + 2] = (flags & kFlagWantSw) ? s[b] : 0.0f;
+        if (crp_out)
+            memcpy(crp_out + crp_offsets[b], c->h_crp.data() + D[b].crp_off, (size_t)D[b].rows * D[b].wp * sizeof(uint32_t));
+    }
+    return ACOSS_OK;
+}
+
+static int dp_unpacked(acoss_ctx* c, const uint8_t* S, int32_t rows, int32_t cols, uint32_t flags, float out[3]) {
+    if (rows < 0 || cols < 0) return fail(ACOSS_ERR_ARG, "negative shape");
+    out[0] = out[1] = out[2] = 0.0f;
+    if (rows == 0 || cols == 0) return ACOSS_OK;
+    if (!S) return fail(ACOSS_ERR_ARG, "S is null");
+    const int wp = (cols + 31) / 32;
+    std::vector<uint32_t> packed((size_t)rows * wp, 0u);
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < cols; ++j)
+            // SequenceAlignment.c tests S == 1 (qmax/dmax) or S > 0 (Match/Delta); the CRP is {0,1}
+            if (S[(size_t)i * cols + j]) packed[(size_t)i * wp + (j >> 5)] |= 1u << (j & 31);
+    const int64_t off = 0;
+    return acoss_dp_packed(c, packed.data(), &off, &rows, &cols, 1, flags, out);
+}
+
+int acoss_qmax(acoss_ctx* c, const uint8_t* S, int32_t M, int32_t N, float* result) {
+    if (!result) return fail(ACOSS_ERR_ARG, "result is null");
+    float o[3];
+    int rc = dp_unpacked(c, S, M, N, kFlagDmaxClean, o);
+    *result = o[0];
+    return rc;
+}
+
+int acoss_dmax(acoss_ctx* c, const uint8_t* S, int32_t M, int32_t N, float* result) {
+    if (!result) return fail(ACOSS_ERR_ARG, "result is null");
+    float o[3];
+    int rc = dp_unpacked(c, S, M, N, kFlagDmaxClean, o);
+    *result = o[1];
+    return rc;
+}
+
+int acoss_qmax_dmax(acoss_ctx* c, const uint8_t* S, int32_t M, int32_t N, float* qmax_result, float* dmax_result) {
+    float o[3];
+    int rc = dp_unpacked(c, S, M, N, 0u, o);
+    if (qmax_result) *qmax_result = o[0];
+    if (dmax_result) *dmax_result = o[1];
+    return rc;
+}
+
+int acoss_swconstrained(acoss_ctx* c, const uint8_t* S, int32_t N, int32_t M, float* result) {
+    if (!result) return fail(ACOSS_ERR_ARG, "result is null");
+    float o[3];
+    int rc = dp_unpacked(c, S, N, M, kFlagDmaxClean | kFlagWantSw, o);
+    *result = o[2];
+    return rc;
+}
+
+int64_t acoss_kernel_launches(acoss_ctx* c) { return c ? c->launches : 0; }
+void acoss_reset_counters(acoss_ctx* c) {
+    if (c) c->launches = 0;
+}
+
+int acoss_last_stage_ms(acoss_ctx* c, float out[5]) {
+    if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
+    if (!c->have_stage_ms) return fail(ACOSS_ERR_STATE, "no acoss_serra09_pairs call yet");
+    for (int s = 0; s < 5; ++s) out[s] = c->stage_ms[s];
+    return ACOSS_OK;
+}
+
+}  // extern "C"

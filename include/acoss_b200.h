@@ -1,0 +1,146 @@
+/*
+ * acoss_b200.h -- C ABI of libacoss_b200.so: the B200 (sm_100a) replacement for the
+ * native + numpy arithmetic of acoss's all-pairs Serra09 scoring path.
+ *
+ * Every entry point is plain C (pointers + sizes, no torch / C++ types), returns an
+ * int status (0 = ok, <0 = error, message through acoss_last_error()) and never throws.
+ * All pointers are HOST pointers unless stated; the library owns its device memory.
+ * One context per (device, host thread); calls on one context are serialised by the caller.
+ *
+ * What each entry point replaces in the reference (paths relative to the acoss tree):
+ *
+ *   acoss_upload_songs      the per-process feature cache of Serra09.load_features
+ *                           (benchmarking/Serra09.py:96-156: 'chroma' (bins, L) and
+ *                           'gchroma' (bins,) per song), packed into one arena
+ *   acoss_serra09_pairs     the per-pair body of Serra09.similarity
+ *                           (benchmarking/Serra09.py:165-175): get_oti
+ *                           (CRPUtils.py:109-136) -> np.roll (:167) -> get_csm
+ *                           (CRPUtils.py:67-84) -> sliding_csm (:24-45) ->
+ *                           csm_to_binary_mutual (:201-219) -> qmax / dmax
+ *                           (pySeqAlign.pyx:14-23 -> SequenceAlignment.c:113-180)
+ *   acoss_align_dense       the tail of EarlySNF.similarity (benchmarking/EarlySNF.py:86-90)
+ *                           and EarlySNF_Old.py:200-218: a caller-supplied dense M x N
+ *                           dissimilarity -> csm_to_binary[_mutual] -> qmax/dmax/swconstrained
+ *   acoss_qmax / acoss_dmax / acoss_swconstrained
+ *                           the Cython FFI itself (pySeqAlign.pyx:7-23): S uint8 [M*N],
+ *                           same argument order and return value; the caller's float D
+ *                           table is not needed (and not filled)
+ *   acoss_dp_packed         batched qmax/dmax/sw over caller-supplied bit-packed CRPs
+ */
+#ifndef ACOSS_B200_H
+#define ACOSS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct acoss_ctx acoss_ctx;
+
+/* status codes */
+#define ACOSS_OK 0
+#define ACOSS_ERR_ARG (-1)     /* bad argument (null pointer, negative size, index out of range) */
+#define ACOSS_ERR_CUDA (-2)    /* a CUDA runtime call or kernel failed */
+#define ACOSS_ERR_STATE (-3)   /* songs not uploaded yet / context destroyed */
+#define ACOSS_ERR_NOMEM (-4)
+
+/* feature dtype of the arena handed to acoss_upload_songs */
+#define ACOSS_F32 0            /* hpcp / mfcc_htk (preprocess/features.py:209-275,418-470) */
+#define ACOSS_F64 1            /* crema (preprocess/features.py:277-296) */
+
+/* flags for the scoring entry points */
+#define ACOSS_FLAG_NO_OTI       (1u << 0) /* skip OTI + roll (mfcc path, Serra09.py:177-180) */
+#define ACOSS_FLAG_DMAX_CLEAN   (1u << 1) /* dmax on a zeroed table (ChenFusion.py:66); default is the
+                                             table left behind by qmax, as Serra09.py:173-175 does */
+#define ACOSS_FLAG_NO_SWAP      (1u << 2) /* keep rows = first song of the pair (debug CRP dumps are then
+                                             in the reference's orientation); by default the shorter song
+                                             is put on the columns (the DPs are transpose-invariant) */
+#define ACOSS_FLAG_NON_MUTUAL   (1u << 3) /* csm_to_binary instead of csm_to_binary_mutual (row kNN only) */
+#define ACOSS_FLAG_WANT_SW      (1u << 4) /* also run the constrained Smith-Waterman DP */
+
+const char* acoss_last_error(void);
+int acoss_version(void);
+
+/* Create / destroy a context bound to CUDA device `device`. Fails (never falls back to the
+ * CPU) when there is no usable device. */
+int acoss_create(acoss_ctx** out, int device);
+int acoss_destroy(acoss_ctx* ctx);
+
+/*
+ * Upload all songs once. frames: frame-major arena [total_frames][bins] of `dtype`
+ * (song s occupies rows offsets[s] .. offsets[s]+lengths[s]-1; this is chroma.T of the
+ * reference's (bins, L) array, so no transposition happens on the device).
+ * gchroma: [n_songs][bins] float64 (Serra09.py:24-28,101-102) or NULL when every call
+ * will pass ACOSS_FLAG_NO_OTI.  bins <= 16.
+ */
+int acoss_upload_songs(acoss_ctx* ctx, const void* frames, int dtype,
+                       const int64_t* offsets, const int32_t* lengths,
+                       int32_t n_songs, int32_t bins, const double* gchroma);
+
+/*
+ * Score P song pairs. pairs: [P][2] int32 song indices (i, j) exactly as
+ * CoverAlgorithm.similarity receives them (CoverAlgorithm.py:117, Serra09.py:158-162).
+ * m: embedding window (Serra09.py:87), kappa: neighbour fraction (0 < kappa < 1).
+ * Outputs (each [P], any may be NULL):
+ *   qmax_raw, dmax_raw, sw_raw : the DP maxima exactly as qmax()/dmax()/swconstrained()
+ *                                return them (NOT yet divided by M+N, Serra09.py:174-175)
+ *   oti_out                    : the optimal transposition index used
+ *   shape_out [P][2]           : (M, N) = (L_i-m+1, L_j-m+1)
+ * Debug CRP dump (crp_out may be NULL): pair p's packed CRP is written at word offset
+ * crp_offsets[p]: rows x ceil(cols/32) uint32, bit t of word w of row r = CRP[r][32w+t].
+ * With ACOSS_FLAG_NO_SWAP rows = M, cols = N; otherwise crp_swapped_out[p] (may be NULL)
+ * tells whether the stored matrix is the transpose.
+ */
+int acoss_serra09_pairs(acoss_ctx* ctx, const int32_t* pairs, int64_t P,
+                        int32_t m, double kappa, uint32_t flags,
+                        float* qmax_raw, float* dmax_raw, float* sw_raw,
+                        int32_t* oti_out, int32_t* shape_out,
+                        uint32_t* crp_out, const int64_t* crp_offsets, int32_t* crp_swapped_out);
+
+/*
+ * Dense entry (EarlySNF.py:86-90): B dense dissimilarity matrices of `dtype` (ACOSS_F32 /
+ * ACOSS_F64; the reference's fused matrix is float64), matrix b is rows[b] x cols[b]
+ * row-major at csm + csm_offsets[b] (elements).  Binarises with
+ * k_row = round(kappa*cols), k_col = round(kappa*rows) (CRPUtils.py:186-199,219) and
+ * runs the DPs.  out: [B][3] = qmax, dmax, sw maxima (sw only with ACOSS_FLAG_WANT_SW, else 0).
+ */
+int acoss_align_dense(acoss_ctx* ctx, const void* csm, int dtype, const int64_t* csm_offsets,
+                      const int32_t* rows, const int32_t* cols, int32_t B,
+                      double kappa, uint32_t flags, float* out,
+                      uint32_t* crp_out, const int64_t* crp_offsets);
+
+/*
+ * Batched DPs over caller-supplied packed CRPs (same packing as the debug dump).
+ * out: [B][3] = qmax, dmax, sw.
+ */
+int acoss_dp_packed(acoss_ctx* ctx, const uint32_t* crp, const int64_t* crp_offsets,
+                    const int32_t* rows, const int32_t* cols, int32_t B,
+                    uint32_t flags, float* out);
+
+/*
+ * Drop-in equivalents of pySeqAlign.qmax / dmax / swconstrained (pySeqAlign.pyx:7-23):
+ * S is the unpacked uint8 matrix, row-major.  qmax/dmax: S is M x N (rows, cols);
+ * swconstrained: S is N x M (its first int is the row count, as in
+ * SequenceAlignment.c:73).  acoss_dmax scores a zeroed table; the Serra09 call pattern
+ * (qmax then dmax on the same table) is acoss_qmax_dmax.  Inputs too small for the
+ * recurrence return 0.0 like the reference (SequenceAlignment.c:78-80,117-119,151-153).
+ */
+int acoss_qmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, float* result);
+int acoss_dmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, float* result);
+int acoss_qmax_dmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, float* qmax_result, float* dmax_result);
+int acoss_swconstrained(acoss_ctx* ctx, const uint8_t* S, int32_t N, int32_t M, float* result);
+
+/* Counters for bench.py: kernels launched by this context since creation / last reset. */
+int64_t acoss_kernel_launches(acoss_ctx* ctx);
+void acoss_reset_counters(acoss_ctx* ctx);
+
+/* Device time (ms, CUDA events on the context's stream) spent in each stage during the
+ * last acoss_serra09_pairs call: out[0]=oti, [1]=threshold sweeps, [2]=crp sweep, [3]=dp,
+ * [4]=whole call on the stream.  Returns ACOSS_ERR_STATE before the first call. */
+int acoss_last_stage_ms(acoss_ctx* ctx, float out[5]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACOSS_B200_H */
