@@ -48,6 +48,7 @@ SIGNATURES = {
     "acoss_dmax": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p]),
     "acoss_qmax_dmax": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p, _c_f32p]),
     "acoss_swconstrained": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p]),
+    "acoss_set_option": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64]),
     "acoss_kernel_launches": (ctypes.c_int64, [ctypes.c_void_p]),
     "acoss_reset_counters": (None, [ctypes.c_void_p]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
@@ -75,7 +76,20 @@ def load_library(path: str | None = None) -> ctypes.CDLL:
     return lib
 
 
-def pack_songs(songs):
+def _host_array(shape, dtype, pinned):
+    """numpy array, in page-locked host memory when asked (torch is only the allocator here)."""
+    if pinned:
+        try:
+            import torch
+            if torch.cuda.is_available():
+                t = torch.empty(tuple(shape), dtype=getattr(torch, np.dtype(dtype).name), pin_memory=True)
+                return t.numpy()
+        except Exception:
+            pass
+    return np.empty(shape, dtype=dtype)
+
+
+def pack_songs(songs, pinned=False):
     """songs: list of dicts with 'chroma' (bins, L) [and 'gchroma' (bins,)] as Serra09.load_features
     returns them (Serra09.py:154).  Returns (frames [total, bins], offsets i64, lengths i32,
     gchroma f64 [n, bins] or None)."""
@@ -86,7 +100,7 @@ def pack_songs(songs):
     if len(songs) > 1:
         offsets[1:] = np.cumsum(lengths[:-1].astype(np.int64))
     total = int(lengths.sum())
-    frames = np.empty((max(total, 1), bins), dtype=dt)
+    frames = _host_array((max(total, 1), bins), dt, pinned)
     for s, o, n in zip(songs, offsets, lengths):
         frames[o:o + n] = s["chroma"].T
     g = None
@@ -281,6 +295,9 @@ class Context:
         self._check(self.lib.acoss_qmax_dmax(self._h, _ptr(S, _c_u8p), int(M), int(N), ctypes.byref(q), ctypes.byref(d)),
                     "acoss_qmax_dmax")
         return float(q.value), float(d.value)
+
+    def set_option(self, name, value):
+        self._check(self.lib.acoss_set_option(self._h, name.encode(), int(value)), "acoss_set_option")
 
     # ------------------------------------------------------------------ accounting
     def kernel_launches(self):

@@ -123,6 +123,11 @@ struct acoss_ctx {
     DevBuf dense_in, dense_desc, dense_starts;
     PinBuf h_stage;
     std::vector<uint32_t> h_crp;
+    // test/tuning knobs (acoss_set_option)
+    int opt_force_wide = 0;      // send every sweep item through the 256-thread kernels
+    int opt_force_gscratch = 0;  // ring + strip in global scratch even when shared memory would do
+    int opt_dp_max_cpl = 16;     // widest DP kernel allowed (4, 8, 16): narrower forces column blocks
+    int opt_chunk_pairs = 1 << 18;
     // accounting
     int64_t launches = 0;
     float stage_ms[5] = {0, 0, 0, 0, 0};
@@ -132,7 +137,6 @@ struct acoss_ctx {
 
 namespace {
 
-constexpr int kMaxChunkPairs = 1 << 18;
 constexpr int64_t kMaxChunkSepDoubles = (int64_t)1 << 28;  // 2 GiB
 constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
 constexpr int kCounterSlots = 16;
@@ -152,7 +156,7 @@ int launch_sweep(acoss_ctx* c, const uint32_t* d_items, int n_items, int Wmax, i
     const size_t fixed = sweep_smem_fixed_bytes(Wmax, BINS);
     const size_t var = (size_t)(RD + (MODE == 0 ? R : 0)) * Wmax * sizeof(double);
     const size_t budget = (size_t)c->max_smem - 1024;  // static shared + launch reserve
-    const bool use_g = fixed + var > budget;
+    const bool use_g = (fixed + var > budget) || c->opt_force_gscratch;
     const size_t smem = use_g ? fixed : fixed + var;
     CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
@@ -226,18 +230,19 @@ int run_dp_lists(acoss_ctx* c, const ItemLists& L, const uint32_t* d_items_base,
     return ACOSS_OK;
 }
 
-void classify_dp(ItemLists& L, uint32_t p, int cols) {
-    if (cols <= 128)
-        L.dp4.push_back(p);
-    else if (cols <= 256)
-        L.dp8.push_back(p);
-    else
-        L.dp16.push_back(p);
+int dp_cpl(const acoss_ctx* c, int cols) {
+    int cpl = cols <= 128 ? 4 : (cols <= 256 ? 8 : 16);
+    return std::min(cpl, c->opt_dp_max_cpl);
 }
 
-int64_t bnd_records(int rows, int cols) {
-    // wide plots (more than one 512-column block in the CPL=16 kernel) need the hand-over scratch
-    return cols > 512 ? (int64_t)rows * 2 * 2 : 0;
+void classify_dp(const acoss_ctx* c, ItemLists& L, uint32_t p, int cols) {
+    const int cpl = dp_cpl(c, cols);
+    (cpl == 4 ? L.dp4 : (cpl == 8 ? L.dp8 : L.dp16)).push_back(p);
+}
+
+int64_t bnd_records(const acoss_ctx* c, int rows, int cols) {
+    // plots wider than one 32*CPL-column block need the hand-over scratch (2 buffers x 2 int4 per row)
+    return cols > 32 * dp_cpl(c, cols) ? (int64_t)rows * 2 * 2 : 0;
 }
 
 template <int BINS>
@@ -269,7 +274,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         w.pad0 = 0;
         w.sep_off = sep_total;
         w.crp_off = crp_total;
-        const int64_t br = bnd_records(w.crp_rows, w.crp_cols);
+        const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
         if (ok) {
@@ -280,7 +285,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             for (int o = 0; o < 2; ++o) {
                 if (o == 1 && nonmutual) break;
                 const int Lc = o ? w.Li : w.Lj;
-                if (Lc <= wA) {
+                if (Lc <= wA && !c->opt_force_wide) {
                     L.thrA.push_back((uint32_t)p * 2 + o);
                 } else {
                     L.thrB.push_back((uint32_t)p * 2 + o);
@@ -288,14 +293,14 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
                 }
             }
             const int Lc = w.swap ? w.Li : w.Lj;
-            if (Lc <= wA) {
+            if (Lc <= wA && !c->opt_force_wide) {
                 L.crpA.push_back((uint32_t)p);
             } else {
                 L.crpB.push_back((uint32_t)p);
                 L.crpB_w = std::max(L.crpB_w, (Lc + wB - 1) / wB * wB);
             }
         }
-        classify_dp(L, (uint32_t)p, w.crp_cols);
+        classify_dp(c, L, (uint32_t)p, w.crp_cols);
     }
     // ---- device buffers
     CU(c->pairs.reserve((size_t)n * sizeof(PairWork)));
@@ -523,7 +528,7 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
         // cut a chunk whose scratch fits the budget
         int n = 0;
         int64_t sep = 0, crp = 0;
-        while (p0 + n < P && n < kMaxChunkPairs) {
+        while (p0 + n < P && n < c->opt_chunk_pairs) {
             const int Li = c->h_len[pairs[2 * (p0 + n)]], Lj = c->h_len[pairs[2 * (p0 + n) + 1]];
             const int64_t M = std::max(Li - m + 1, 0), N = std::max(Lj - m + 1, 0);
             const int64_t s2 = M + N, c2 = std::max(M, N) * ((std::min(M, N) + 31) / 32 + 1);
@@ -562,10 +567,10 @@ int acoss_dp_packed(acoss_ctx* c, const uint32_t* crp, const int64_t* crp_offset
         w.crp_wp = (cols[b] + 31) / 32;
         w.crp_off = crp_total;
         crp_total += (int64_t)w.crp_rows * w.crp_wp;
-        const int64_t br = bnd_records(w.crp_rows, w.crp_cols);
+        const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
-        classify_dp(L, (uint32_t)b, w.crp_cols);
+        classify_dp(c, L, (uint32_t)b, w.crp_cols);
     }
     CU(c->pairs.reserve((size_t)B * sizeof(PairWork)));
     CU(c->crp.reserve((size_t)std::max<int64_t>(crp_total, 1) * sizeof(uint32_t)));
@@ -640,10 +645,10 @@ int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* c
         w.crp_cols = d.cols;
         w.crp_wp = d.wp;
         w.crp_off = crp_total;
-        const int64_t br = bnd_records(w.crp_rows, w.crp_cols);
+        const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
-        classify_dp(L, (uint32_t)b, w.crp_cols);
+        classify_dp(c, L, (uint32_t)b, w.crp_cols);
         el_total += (int64_t)d.rows * d.cols;
         sep_total += (int64_t)d.rows + d.cols;
         crp_total += (int64_t)d.rows * d.wp;
@@ -762,6 +767,24 @@ int acoss_swconstrained(acoss_ctx* c, const uint8_t* S, int32_t N, int32_t M, fl
     int rc = dp_unpacked(c, S, N, M, kFlagDmaxClean | kFlagWantSw, o);
     *result = o[2];
     return rc;
+}
+
+int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
+    if (!c || !name) return fail(ACOSS_ERR_ARG, "null argument");
+    const std::string n(name);
+    if (n == "force_wide_sweep")
+        c->opt_force_wide = value != 0;
+    else if (n == "force_gscratch")
+        c->opt_force_gscratch = value != 0;
+    else if (n == "dp_max_cpl") {
+        if (value != 4 && value != 8 && value != 16) return fail(ACOSS_ERR_ARG, "dp_max_cpl must be 4, 8 or 16");
+        c->opt_dp_max_cpl = (int)value;
+    } else if (n == "chunk_pairs") {
+        if (value < 1) return fail(ACOSS_ERR_ARG, "chunk_pairs must be >= 1");
+        c->opt_chunk_pairs = (int)std::min<int64_t>(value, 1 << 20);
+    } else
+        return fail(ACOSS_ERR_ARG, "unknown option %s", name);
+    return ACOSS_OK;
 }
 
 int64_t acoss_kernel_launches(acoss_ctx* c) { return c ? c->launches : 0; }

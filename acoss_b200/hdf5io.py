@@ -1,0 +1,379 @@
+"""Minimal self-contained HDF5 writer / reader (no h5py, pytables or libhdf5 exists on either
+machine image), enough for the artefacts of the all-pairs path that the reference writes with
+deepdish (benchmarking/CoverAlgorithm.py:160,183,264,292): nested dicts of numpy arrays and
+scalars.
+
+File layout produced (HDF5 file-format spec 1.x, the oldest and most widely readable forms):
+  superblock version 0; every dict is an old-style group (object header v1 with a Symbol Table
+  message -> v1 B-tree with one leaf -> one symbol-table node -> local heap of names);
+  every ndarray is a dataset with a contiguous, uncompressed, little-endian layout
+  (Dataspace v1, Datatype v1, Data Layout v3 messages) carrying PyTables-style
+  CLASS/VERSION/TITLE/FLAVOR attributes; str / int / float / bool scalars are attributes of
+  the enclosing group, as deepdish stores them.
+The reader understands exactly those structures (plus object-header continuation blocks and
+multi-level group B-trees), i.e. it reads files written here and other plain contiguous HDF5
+files; chunked / compressed datasets (deepdish's default blosc CArrays) are reported as
+unsupported rather than misread.
+"""
+from __future__ import annotations
+
+import struct
+
+import numpy as np
+
+UNDEF = 0xFFFFFFFFFFFFFFFF
+SIGNATURE = b"\x89HDF\r\n\x1a\n"
+INTERNAL_K = 16
+
+MSG_DATASPACE, MSG_DATATYPE, MSG_LAYOUT, MSG_ATTRIBUTE, MSG_CONT, MSG_SYMTAB = 0x1, 0x3, 0x8, 0xC, 0x10, 0x11
+
+
+def _pad8(b: bytes) -> bytes:
+    return b + b"\0" * (-len(b) % 8)
+
+
+# ---------------------------------------------------------------------------- datatype / dataspace
+def _datatype_msg(dt: np.dtype) -> bytes:
+    dt = np.dtype(dt)
+    if dt.kind == "f":
+        size = dt.itemsize
+        if size == 4:
+            props = struct.pack("<HHBBBBI", 0, 32, 23, 8, 0, 23, 127)
+            sign = 31
+        elif size == 8:
+            props = struct.pack("<HHBBBBI", 0, 64, 52, 11, 0, 52, 1023)
+            sign = 63
+        else:
+            raise TypeError("unsupported float size %d" % size)
+        return struct.pack("<BBBBI", 0x11, 0x20, sign, 0, size) + props
+    if dt.kind in "iub":
+        size = dt.itemsize
+        signed = 0x08 if dt.kind == "i" else 0x00
+        return struct.pack("<BBBBI", 0x10, signed, 0, 0, size) + struct.pack("<HH", 0, size * 8)
+    if dt.kind == "S":
+        return struct.pack("<BBBBI", 0x13, 0x00, 0, 0, max(dt.itemsize, 1))
+    raise TypeError("unsupported dtype %s" % dt)
+
+
+def _dataspace_msg(shape) -> bytes:
+    rank = len(shape)
+    return struct.pack("<BBBB4x", 1, rank, 0, 0) + b"".join(struct.pack("<Q", int(d)) for d in shape)
+
+
+def _message(mtype: int, data: bytes) -> bytes:
+    data = _pad8(data)
+    return struct.pack("<HHB3x", mtype, len(data), 0) + data
+
+
+def _attribute_msg(name: str, value) -> bytes:
+    nm = name.encode("utf8") + b"\0"
+    if isinstance(value, (bytes, str)):
+        raw = value.encode("utf8") if isinstance(value, str) else value
+        arr = np.array(raw + b"\0", dtype="S%d" % (len(raw) + 1))
+    elif isinstance(value, (bool, np.bool_)):
+        arr = np.array(int(value), dtype=np.uint8)
+    elif isinstance(value, (int, np.integer)):
+        arr = np.array(int(value), dtype=np.int64)
+    elif isinstance(value, (float, np.floating)):
+        arr = np.array(float(value), dtype=np.float64)
+    else:
+        raise TypeError("unsupported attribute type %r" % type(value))
+    dtm = _datatype_msg(arr.dtype)
+    dsm = _dataspace_msg(())
+    body = struct.pack("<BBHHH", 1, 0, len(nm), len(dtm), len(dsm)) + _pad8(nm) + _pad8(dtm) + _pad8(dsm) + arr.tobytes()
+    return _message(MSG_ATTRIBUTE, body)
+
+
+def _object_header(messages) -> bytes:
+    body = b"".join(messages)
+    return struct.pack("<BBHII4x", 1, 0, len(messages), 1, len(body)) + body
+
+
+# ---------------------------------------------------------------------------- writer
+class _Writer:
+    def __init__(self, f, leaf_k):
+        self.f = f
+        self.leaf_k = leaf_k
+
+    def _append(self, b: bytes) -> int:
+        pos = self.f.tell()
+        if pos % 8:
+            self.f.write(b"\0" * (-pos % 8))
+            pos = self.f.tell()
+        self.f.write(b)
+        return pos
+
+    def write_dataset(self, arr: np.ndarray) -> int:
+        arr = np.asarray(arr)
+        if arr.dtype.kind == "U":
+            arr = np.char.encode(arr, "utf8")
+        if arr.dtype.byteorder == ">":
+            arr = arr.astype(arr.dtype.newbyteorder("<"))
+        if not arr.flags.c_contiguous:
+            arr = np.ascontiguousarray(arr)
+        nbytes = arr.size * arr.dtype.itemsize
+        addr = UNDEF
+        if nbytes:
+            pos = self.f.tell()
+            if pos % 8:
+                self.f.write(b"\0" * (-pos % 8))
+            addr = self.f.tell()
+            self.f.write(memoryview(arr).cast("B"))  # no copy: the score matrices can be ~1 GB
+        msgs = [_message(MSG_DATASPACE, _dataspace_msg(arr.shape)),
+                _message(MSG_DATATYPE, _datatype_msg(arr.dtype)),
+                _message(MSG_LAYOUT, struct.pack("<BBQQ", 3, 1, addr, nbytes)),
+                _attribute_msg("CLASS", "ARRAY"), _attribute_msg("VERSION", "2.4"),
+                _attribute_msg("TITLE", ""), _attribute_msg("FLAVOR", "numpy")]
+        return self._append(_object_header(msgs))
+
+    def write_group(self, d: dict, root=False):
+        """Returns (object header address, btree address, heap address)."""
+        children = []  # (name bytes, header addr, is_group, btree, heap)
+        attrs = [_attribute_msg("CLASS", "GROUP"), _attribute_msg("VERSION", "1.0"), _attribute_msg("TITLE", "")]
+        if root:
+            attrs.append(_attribute_msg("PYTABLES_FORMAT_VERSION", "2.1"))
+        for key, val in d.items():
+            name = str(key)
+            if isinstance(val, dict):
+                h, bt, hp = self.write_group(val)
+                children.append((name.encode("utf8"), h, True, bt, hp))
+            elif isinstance(val, (str, bytes, bool, int, float, np.integer, np.floating, np.bool_)):
+                attrs.append(_attribute_msg(name, val))
+            elif val is None:
+                attrs.append(_attribute_msg(name, "__none__"))
+            else:
+                children.append((name.encode("utf8"), self.write_dataset(np.asarray(val)), False, 0, 0))
+        children.sort(key=lambda c: c[0])
+        # local heap: offset 0 holds the empty string
+        heap = bytearray(b"\0" * 8)
+        offs = []
+        for nm, *_ in children:
+            offs.append(len(heap))
+            heap += _pad8(nm + b"\0")
+        free_off = len(heap)
+        heap += struct.pack("<QQ", 1, 16)  # one free block closing the segment (next = 1: end of list)
+        heap_data_addr = self._append(bytes(heap))
+        heap_addr = self._append(b"HEAP" + struct.pack("<B3xQQQ", 0, len(heap), free_off, heap_data_addr))
+        # symbol table node
+        if len(children) > 2 * self.leaf_k:
+            raise ValueError("group with %d entries exceeds the leaf node capacity" % len(children))
+        snod = bytearray(b"SNOD" + struct.pack("<BBH", 1, 0, len(children)))
+        for (nm, h, is_group, bt, hp), off in zip(children, offs):
+            if is_group:
+                snod += struct.pack("<QQII", off, h, 1, 0) + struct.pack("<QQ", bt, hp)
+            else:
+                snod += struct.pack("<QQII", off, h, 0, 0) + b"\0" * 16
+        snod += b"\0" * (8 + 2 * self.leaf_k * 40 - len(snod))
+        snod_addr = self._append(bytes(snod))
+        # B-tree: one leaf-level node
+        nent = 1 if children else 0
+        bt = bytearray(b"TREE" + struct.pack("<BBHQQ", 0, 0, nent, UNDEF, UNDEF))
+        if children:
+            bt += struct.pack("<QQQ", 0, snod_addr, offs[-1])
+        bt += b"\0" * (24 + (2 * INTERNAL_K + 1) * 8 + 2 * INTERNAL_K * 8 - len(bt))
+        bt_addr = self._append(bytes(bt))
+        hdr = self._append(_object_header([_message(MSG_SYMTAB, struct.pack("<QQ", bt_addr, heap_addr))] + attrs))
+        return hdr, bt_addr, heap_addr
+
+
+def _max_entries(d):
+    n = sum(1 for v in d.values() if isinstance(v, dict) or not isinstance(
+        v, (str, bytes, bool, int, float, np.integer, np.floating, np.bool_, type(None))))
+    for v in d.values():
+        if isinstance(v, dict):
+            n = max(n, _max_entries(v))
+    return n
+
+
+def save(path, data: dict):
+    """Write a (nested) dict of numpy arrays / scalars / strings to an HDF5 file."""
+    if not isinstance(data, dict):
+        raise TypeError("top level must be a dict (deepdish stores a dict as the root group's children)")
+    leaf_k = max(4, (_max_entries(data) + 1) // 2)
+    if leaf_k > 32767:
+        raise ValueError("too many entries in one group")
+    with open(path, "wb") as f:
+        f.write(b"\0" * 96)
+        w = _Writer(f, leaf_k)
+        hdr, bt, hp = w.write_group(data, root=True)
+        pos = f.tell()
+        if pos % 8:
+            f.write(b"\0" * (-pos % 8))
+        eof = f.tell()
+        sb = SIGNATURE + struct.pack("<BBBBBBBBHHI", 0, 0, 0, 0, 0, 8, 8, 0, leaf_k, INTERNAL_K, 0)
+        sb += struct.pack("<QQQQ", 0, UNDEF, eof, UNDEF)
+        sb += struct.pack("<QQII", 0, hdr, 1, 0) + struct.pack("<QQ", bt, hp)
+        assert len(sb) == 96
+        f.seek(0)
+        f.write(sb)
+
+
+# ---------------------------------------------------------------------------- reader
+class _Reader:
+    def __init__(self, buf):
+        self.b = buf
+        if bytes(buf[:8]) != SIGNATURE:
+            raise ValueError("not an HDF5 file")
+        ver = buf[8]
+        if ver not in (0, 1):
+            raise NotImplementedError("superblock version %d is not supported by this reader" % ver)
+        if buf[13] != 8 or buf[14] != 8:
+            raise NotImplementedError("only 8-byte offsets / lengths are supported")
+        self.leaf_k, self.internal_k = struct.unpack_from("<HH", buf, 16)
+        base = 24 + (4 if ver == 1 else 0)
+        self.base_addr = struct.unpack_from("<Q", buf, base)[0]
+        self.root_entry = base + 32
+
+    def u64(self, off):
+        return struct.unpack_from("<Q", self.b, off)[0]
+
+    def heap_name(self, heap_addr, off):
+        if bytes(self.b[heap_addr:heap_addr + 4]) != b"HEAP":
+            raise ValueError("bad local heap signature")
+        data_addr = self.u64(heap_addr + 24)
+        start = data_addr + off
+        end = start
+        while self.b[end] != 0:
+            end += 1
+        return bytes(self.b[start:end]).decode("utf8")
+
+    def btree_entries(self, bt_addr, heap_addr, out):
+        if bytes(self.b[bt_addr:bt_addr + 4]) != b"TREE":
+            raise ValueError("bad B-tree signature")
+        node_type, level, nent = struct.unpack_from("<BBH", self.b, bt_addr + 4)
+        if node_type != 0:
+            raise ValueError("not a group B-tree")
+        pos = bt_addr + 24
+        for e in range(nent):
+            child = self.u64(pos + 8)
+            pos += 16
+            if level > 0:
+                self.btree_entries(child, heap_addr, out)
+            else:
+                if bytes(self.b[child:child + 4]) != b"SNOD":
+                    raise ValueError("bad symbol table node signature")
+                nsym = struct.unpack_from("<H", self.b, child + 6)[0]
+                for s in range(nsym):
+                    eoff = child + 8 + 40 * s
+                    name_off, hdr = struct.unpack_from("<QQ", self.b, eoff)
+                    out.append((self.heap_name(heap_addr, name_off), hdr))
+
+    def messages(self, hdr_addr):
+        ver, _, nmsg, _, hsize = struct.unpack_from("<BBHII", self.b, hdr_addr)
+        if ver != 1:
+            raise NotImplementedError("object header version %d is not supported" % ver)
+        blocks = [(hdr_addr + 16, hsize)]
+        msgs = []
+        while blocks and len(msgs) < nmsg:
+            pos, size = blocks.pop(0)
+            end = pos + size
+            while pos + 8 <= end and len(msgs) < nmsg:
+                mtype, msize, _flags = struct.unpack_from("<HHB", self.b, pos)
+                data = self.b[pos + 8:pos + 8 + msize]
+                pos += 8 + msize
+                if mtype == MSG_CONT:
+                    blocks.append(struct.unpack_from("<QQ", data, 0))
+                msgs.append((mtype, data))
+        return msgs
+
+    @staticmethod
+    def parse_datatype(data):
+        cv, b0, b1, _b2, size = struct.unpack_from("<BBBBI", data, 0)
+        cls, ver = cv & 0x0F, cv >> 4
+        if ver not in (1, 2, 3):
+            raise NotImplementedError("datatype version %d" % ver)
+        order = ">" if (b0 & 1) else "<"
+        if cls == 1:
+            return np.dtype("%sf%d" % (order, size))
+        if cls == 0:
+            return np.dtype("%s%s%d" % (order, "i" if (b0 & 0x08) else "u", size))
+        if cls == 3:
+            return np.dtype("S%d" % size)
+        raise NotImplementedError("datatype class %d is not supported" % cls)
+
+    @staticmethod
+    def parse_dataspace(data):
+        ver, rank, flags = struct.unpack_from("<BBB", data, 0)
+        off = 8 if ver == 1 else 4
+        return tuple(struct.unpack_from("<Q", data, off + 8 * i)[0] for i in range(rank))
+
+    def parse_attribute(self, data):
+        ver, _, nsz, dtsz, dssz = struct.unpack_from("<BBHHH", data, 0)
+        if ver != 1:
+            raise NotImplementedError("attribute version %d" % ver)
+        pos = 8
+        name = bytes(data[pos:pos + nsz]).split(b"\0")[0].decode("utf8")
+        pos += nsz + (-nsz % 8)
+        dt = self.parse_datatype(data[pos:pos + dtsz])
+        pos += dtsz + (-dtsz % 8)
+        shape = self.parse_dataspace(data[pos:pos + dssz])
+        pos += dssz + (-dssz % 8)
+        n = int(np.prod(shape)) if shape else 1
+        arr = np.frombuffer(bytes(data[pos:pos + n * dt.itemsize]), dtype=dt, count=n).reshape(shape)
+        if dt.kind == "S":
+            val = arr.reshape(-1)[0].split(b"\0")[0].decode("utf8") if n == 1 else arr
+        elif shape == ():
+            val = arr.item()
+        else:
+            val = arr
+        return name, val
+
+    def read_object(self, hdr_addr, mmap_arrays):
+        msgs = self.messages(hdr_addr)
+        symtab = [d for t, d in msgs if t == MSG_SYMTAB]
+        if symtab:
+            bt, hp = struct.unpack_from("<QQ", symtab[0], 0)
+            entries = []
+            self.btree_entries(bt, hp, entries)
+            out = {}
+            for name, h in entries:
+                out[name] = self.read_object(h, mmap_arrays)
+            for t, d in msgs:
+                if t == MSG_ATTRIBUTE:
+                    name, val = self.parse_attribute(d)
+                    if name in ("CLASS", "VERSION", "TITLE", "PYTABLES_FORMAT_VERSION", "FILTERS"):
+                        continue
+                    out[name] = None if (isinstance(val, str) and val == "__none__") else val
+            return out
+        dt = shape = None
+        layout = None
+        for t, d in msgs:
+            if t == MSG_DATATYPE:
+                dt = self.parse_datatype(d)
+            elif t == MSG_DATASPACE:
+                shape = self.parse_dataspace(d)
+            elif t == MSG_LAYOUT:
+                layout = d
+        if dt is None or shape is None or layout is None:
+            raise ValueError("object at %d is neither a group nor a dataset" % hdr_addr)
+        lver, lcls = layout[0], layout[1]
+        if lver != 3:
+            raise NotImplementedError("data layout version %d" % lver)
+        n = int(np.prod(shape)) if shape else 1
+        if lcls == 1:
+            addr, _size = struct.unpack_from("<QQ", layout, 2)
+            if addr == UNDEF or n == 0:
+                arr = np.zeros(shape, dt)
+            else:
+                arr = np.frombuffer(self.b, dtype=dt, count=n, offset=addr + self.base_addr).reshape(shape)
+        elif lcls == 0:
+            size = struct.unpack_from("<H", layout, 2)[0]
+            arr = np.frombuffer(bytes(layout[4:4 + size]), dtype=dt, count=n).reshape(shape)
+        else:
+            raise NotImplementedError("chunked / compressed datasets (e.g. deepdish's default blosc CArrays) "
+                                      "cannot be read without an HDF5 library")
+        if not mmap_arrays:
+            arr = np.array(arr)
+        if dt.kind == "S" and shape == ():
+            return arr.item().split(b"\0")[0].decode("utf8")
+        return arr
+
+    def root(self, mmap_arrays):
+        hdr = self.u64(self.root_entry + 8)
+        return self.read_object(hdr, mmap_arrays)
+
+
+def load(path, mmap_arrays=False):
+    """Read an HDF5 file written by `save` (or any plain contiguous HDF5 file) into nested dicts."""
+    buf = np.memmap(path, dtype=np.uint8, mode="r")
+    return _Reader(buf).root(mmap_arrays)

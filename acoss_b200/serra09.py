@@ -1,0 +1,226 @@
+"""Drop-in mirror of the reference's Serra09 plugin (benchmarking/Serra09.py:73-196) whose
+per-pair arithmetic runs on the GPU through the C ABI (acoss_b200._native).
+
+Same constructor keywords, `load_features(i)` returns the same per-song dict
+({'gchroma', 'chroma', 'mfcc', 'ssms'}), `similarity(idxs)` returns the same dict of float64
+score arrays and writes `self.Ds[key][i][j]`.  The reference's per-pair Python loop
+(Serra09.py:161) disappears: the whole (P, 2) index array goes to the device in one call.
+
+Out of scope: the 'ssms_scatter_*' similarity types need kymatio's
+Scattering2D; they are not produced (the keys are omitted, documented in DESIGN.md).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import _native
+from .cover_algorithm import CoverAlgorithm
+
+
+def global_chroma(chroma):
+    """Global chroma of a (frames, bins) array (benchmarking/Serra09.py:24-28)."""
+    if chroma.shape[1] not in [12, 24, 36]:
+        raise IOError("Wrong axis for the input chroma array. Expected shape '(frame_size, bin_size)'")
+    global_chroma = np.sum(chroma, axis=0)
+    return global_chroma / np.max(global_chroma)
+
+
+def sync_aggregate(data, fac, aggregate):
+    """librosa.util.sync(data, np.arange(0, n, fac), aggregate=...) for a (d, n) array
+    (Serra09.py:104,110): frames [fac*k, min(fac*(k+1), n)) are aggregated along the time axis."""
+    d, n = data.shape
+    starts = np.arange(0, n, fac)
+    out = np.empty((d, len(starts)), dtype=data.dtype, order='F')
+    for k, s in enumerate(starts):
+        out[:, k] = aggregate(data[:, s:min(s + fac, n)], axis=1)
+    return out
+
+
+class Serra09(CoverAlgorithm):
+    """
+    Attributes
+    ----------
+    Same as CoverAlgorithm, plus
+    chroma_type: string
+        Type of chroma to use (key into features)
+    downsample_fac: int
+        The factor by which to downsample the HPCPs with median aggregation
+    m: int
+        Number of frames to stack in a delay embedding
+    kappa: float
+        Fraction of nearest neighbours kept per row / column of the cross-recurrence plot
+    """
+
+    def __init__(self, datapath="features_covers80", chroma_type='crema', shortname='Covers80', oti=True,
+                 kappa=0.095, m=9, downsample_fac=40, do_memmaps=True, cachedir="cache", songs=None, labels=None,
+                 device=0, do_mfcc=True, name="Serra09"):
+        self.oti = oti
+        self.m = m
+        self.chroma_type = chroma_type
+        self.kappa = kappa
+        self.downsample_fac = downsample_fac
+        self.device = device
+        self.do_mfcc = do_mfcc
+        self._ctx = {}        # 'chroma' / 'mfcc' -> (Context, song index -> arena slot)
+        self._packed = {}     # kind -> (song ids, packed host arena): what load_features cached, ready to upload
+        self.last_stage_ms = None
+        similarity_types = ["chroma_qmax", "chroma_dmax"]
+        if do_mfcc:
+            similarity_types += ["mfcc_qmax", "mfcc_dmax"]
+        CoverAlgorithm.__init__(self, name, datapath=datapath, shortname=shortname, cachedir=cachedir,
+                                similarity_types=similarity_types, do_memmaps=do_memmaps, songs=songs, labels=labels)
+
+    # ------------------------------------------------------------------ features
+    def load_features(self, i):
+        """Per-song features as Serra09.load_features computes them (Serra09.py:96-156, chroma and
+        mfcc parts).  Already-prepared songs (a 'chroma' of shape (bins, L) plus 'gchroma', as the
+        synthetic generator makes) pass through unchanged."""
+        if i in self.all_feats:
+            return self.all_feats[i]
+        feats = CoverAlgorithm.load_features(self, i)
+        if 'gchroma' in feats and 'chroma' in feats:
+            ret = {'gchroma': feats['gchroma'], 'chroma': feats['chroma'], 'mfcc': feats.get('mfcc'), 'ssms': None}
+        else:
+            chroma = feats[self.chroma_type]                      # (n_frames, 12)
+            gchroma = global_chroma(chroma)                        # Serra09.py:101-102
+            chroma = sync_aggregate(chroma.T, self.downsample_fac, np.median)   # Serra09.py:104
+            mfcc = None
+            if self.do_mfcc and 'mfcc_htk' in feats:
+                mfcc = np.array(feats['mfcc_htk'])                 # (13, n_frames)
+                mfcc[np.isnan(mfcc)] = 0                           # Serra09.py:107-109
+                mfcc[np.isinf(mfcc)] = 0
+                mfcc = sync_aggregate(mfcc, self.downsample_fac, np.mean)       # Serra09.py:110
+                N = min(chroma.shape[1], mfcc.shape[1])            # Serra09.py:111-114
+                chroma = chroma[:, 0:N]
+                mfcc = mfcc[:, 0:N]
+            ret = {'gchroma': gchroma, 'chroma': chroma, 'mfcc': mfcc, 'ssms': None}
+        self.all_feats[i] = ret
+        return ret
+
+    # ------------------------------------------------------------------ device arena
+    def _context_for(self, kind, song_ids):
+        """Make sure every song in song_ids is in the device arena of `kind`; returns
+        (Context, slot lookup array).  The arena is rebuilt (union of old and new songs) when a
+        call needs songs that are not resident; all_pairwise uploads everything once."""
+        entry = self._ctx.get(kind)
+        need = np.unique(np.asarray(song_ids, dtype=np.int64))
+        if entry is not None:
+            ctx, slot = entry
+            if np.all(slot[need] >= 0):
+                return ctx, slot
+            need = np.union1d(need, np.nonzero(slot >= 0)[0])
+        else:
+            ctx = _native.Context(self.device)
+        cached = self._packed.get(kind)
+        if cached is not None and np.all(np.isin(need, cached[0])):
+            need, packed = cached   # the cached host arena already covers these songs
+        else:
+            songs = []
+            for i in need:
+                f = self.load_features(int(i))
+                if kind == 'chroma':
+                    songs.append({'chroma': np.asarray(f['chroma']), 'gchroma': f['gchroma']})
+                else:
+                    songs.append({'chroma': np.asarray(f['mfcc']), 'gchroma': None})
+            packed = _native.pack_songs(songs, pinned=True)   # host arena, page-locked when a GPU is present
+            self._packed[kind] = (need, packed)
+        ctx.upload(*packed)
+        slot = -np.ones(self.N, dtype=np.int64)
+        slot[need] = np.arange(len(need))
+        self._ctx[kind] = (ctx, slot)
+        return ctx, slot
+
+    def preload(self, song_ids=None):
+        """Upload the features of song_ids (default: all songs) ahead of scoring."""
+        ids = np.arange(self.N) if song_ids is None else song_ids
+        self._context_for('chroma', ids)
+        if self.do_mfcc and self.load_features(int(ids[0]))['mfcc'] is not None:
+            self._context_for('mfcc', ids)
+
+    # ------------------------------------------------------------------ scoring
+    def similarity(self, idxs):
+        """Scores for the (P, 2) song pairs in idxs (Serra09.py:158-196).  Returns
+        {'chroma_qmax', 'chroma_dmax'[, 'mfcc_qmax', 'mfcc_dmax']: float64 (P,)} and stores them
+        in self.Ds[key][i][j] as a side effect."""
+        idxs = np.asarray(idxs).reshape(-1, 2)
+        N = idxs.shape[0]
+        similarities = {}
+        if N == 0:
+            return {s: np.zeros(0) for s in self.similarity_types}
+        kinds = [('chroma', 0)]
+        if self.do_mfcc and self.load_features(int(idxs[0, 0]))['mfcc'] is not None:
+            kinds.append(('mfcc', _native.FLAG_NO_OTI))   # Serra09.py:177-184: no OTI for mfcc
+        stage = {}
+        for kind, flags in kinds:
+            ctx, slot = self._context_for(kind, idxs.reshape(-1))
+            pairs = slot[idxs].astype(np.int32)
+            r = ctx.serra09_pairs(pairs, m=self.m, kappa=self.kappa, flags=flags)
+            MN = r['shape'].sum(axis=1).astype(np.float64)     # M + N (Serra09.py:174-175)
+            MN[MN <= 0] = 1.0
+            similarities['%s_qmax' % kind] = r['qmax_raw'].astype(np.float64) / MN
+            similarities['%s_dmax' % kind] = r['dmax_raw'].astype(np.float64) / MN
+            stage[kind] = ctx.last_stage_ms()
+        self.last_stage_ms = stage
+        if self.do_memmaps or len(self.Ds) > 0:
+            for key in similarities:
+                if key in self.Ds:
+                    self.Ds[key][idxs[:, 0], idxs[:, 1]] = similarities[key]
+        return similarities
+
+    def drop_device_arena(self):
+        """Forget what is resident on the device (the host-side feature cache stays): the next
+        similarity() call uploads again.  bench.py uses it to put the H2D copy inside a timed step."""
+        for kind, (ctx, slot) in list(self._ctx.items()):
+            self._ctx[kind] = (ctx, -np.ones(self.N, dtype=np.int64))
+
+    def host_arena_bytes(self):
+        return sum(sum(a.nbytes for a in packed if a is not None) for _, packed in self._packed.values())
+
+    def kernel_launches(self):
+        return sum(ctx.kernel_launches() for ctx, _ in self._ctx.values())
+
+    def close(self):
+        for ctx, _ in self._ctx.values():
+            ctx.close()
+        self._ctx = {}
+
+
+def main(argv=None):
+    """Command line of benchmarking/Serra09.py:198-244 (same flags)."""
+    import argparse
+    parser = argparse.ArgumentParser(description="Benchmarking with Joan Serra's Cover id algorithm (GPU)",
+                                     formatter_class=argparse.ArgumentDefaultsHelpFormatter)
+    parser.add_argument("-d", '--datapath', type=str, action="store", default='features_covers80',
+                        help="Path to data files")
+    parser.add_argument("-s", "--shortname", type=str, action="store", default="covers80", help="Short name for dataset")
+    parser.add_argument("-c", '--chroma_type', type=str, action="store", default='hpcp',
+                        help="Type of chroma to use for experiments")
+    parser.add_argument("-p", '--parallel', type=int, choices=(0, 1), action="store", default=0,
+                        help="Accepted for compatibility; the GPU path ignores it")
+    parser.add_argument("-n", '--n_cores', type=int, action="store", default=1, help="Accepted for compatibility")
+    parser.add_argument("-r", '--range', type=str, action="store", default="", help="Range of pairs to do, '<w>-<idx>'")
+    parser.add_argument("-f", '--features', type=int, action="store", default=-1, help="Batch index in which to compute features")
+    parser.add_argument("-w", '--wsub', type=int, action="store", default=-1, help="Sub-block size in batch mode")
+    parser.add_argument("-b", '--batch_path', type=str, action="store", default="", help="Prefix of batch files to aggregate")
+    cmd_args = parser.parse_args(argv)
+    do_memmaps = not (len(cmd_args.range) > 0 or cmd_args.features > -1)
+    serra09 = Serra09(cmd_args.datapath, cmd_args.chroma_type, cmd_args.shortname, do_memmaps=do_memmaps)
+    serra09.set_cache2dir("cache2")
+    if len(cmd_args.batch_path) > 0:
+        serra09.load_batches(cmd_args.batch_path)
+        for similarity_type in serra09.Ds.keys():
+            serra09.getEvalStatistics(similarity_type)
+    elif cmd_args.features > -1:
+        serra09.do_batch_features(50, cmd_args.features)
+    elif len(cmd_args.range) > 0:
+        [w, idx] = [int(s) for s in cmd_args.range.split("-")]
+        serra09.do_batch(w, idx, cmd_args.wsub)
+    else:
+        serra09.all_pairwise(cmd_args.parallel, cmd_args.n_cores, symmetric=True)
+        for similarity_type in serra09.Ds.keys():
+            serra09.getEvalStatistics(similarity_type)
+        serra09.cleanup_memmap()
+
+
+if __name__ == '__main__':
+    main()

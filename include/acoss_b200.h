@@ -131,6 +131,10 @@ int acoss_dmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, float* re
 int acoss_qmax_dmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, float* qmax_result, float* dmax_result);
 int acoss_swconstrained(acoss_ctx* ctx, const uint8_t* S, int32_t N, int32_t M, float* result);
 
+/* Test / tuning knobs (results never depend on them): "force_wide_sweep" (0/1),
+ * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "chunk_pairs" (pairs per internal chunk). */
+int acoss_set_option(acoss_ctx* ctx, const char* name, int64_t value);
+
 /* Counters for bench.py: kernels launched by this context since creation / last reset. */
 int64_t acoss_kernel_launches(acoss_ctx* ctx);
 void acoss_reset_counters(acoss_ctx* ctx);

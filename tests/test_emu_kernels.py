@@ -1,0 +1,67 @@
+"""CPU-only: the product's kernel SOURCES compiled with g++ against the SIMT emulator
+(tests/emu/cuda_emu.h) and checked against the golden vectors / the oracle on small cases.
+This validates indexing and synchronisation logic where no GPU exists; the parity tests
+proper are tests/test_gpu_parity.py (real library, real B200)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "emu"))
+
+import parity_checks as pc  # noqa: E402
+from acoss_b200 import _native, synth  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from build_emu import build
+    c = _native.Context(0, build())
+    yield c
+    c.close()
+
+
+def test_emu_golden_pairs_small(ctx, golden):
+    assert pc.check_golden_pairs(ctx, golden, tags=("c", "e"), flag_sets=(_native.FLAG_NO_SWAP, 0)) >= 12
+
+
+def test_emu_golden_dp(ctx, golden):
+    assert pc.check_golden_dp(ctx, golden) == 12
+
+
+def test_emu_options_invariant(ctx):
+    songs, _ = synth.make_song_set("covers80", seed=21, n_songs=4, length_range=(30, 60))
+    pairs = np.array([(0, 1), (1, 2), (2, 3), (3, 0), (0, 2)], np.int32)
+    base = pc.check_options_invariant(ctx, songs, pairs, m=5, kappa=0.1)
+    # and the base itself is right
+    for p, (i, j) in enumerate(pairs):
+        o = pc.oracle_pair(songs, int(i), int(j), 5, 0.1, True)
+        assert np.array_equal(base["crp"][p], o["crp"])
+        assert base["qmax_raw"][p] == o["qmax_raw"] and base["dmax_raw"][p] == o["dmax_raw"]
+
+
+def test_emu_dense(ctx):
+    assert pc.check_dense(ctx, [(20, 37), (45, 33), (5, 4)]) == 3
+
+
+def test_emu_degenerate(ctx):
+    assert pc.check_degenerate(ctx) == 30
+
+
+def test_emu_dp_multiblock(ctx):
+    # plots wider than one column block: hand-over through the boundary scratch
+    rng = np.random.default_rng(4)
+    plots = [(rng.uniform(size=(M, N)) < dens).astype(np.uint8)
+             for (M, N, dens) in [(30, 200, 0.2), (25, 131, 0.4), (40, 129, 0.08), (12, 300, 0.3)]]
+    from oracle import dp
+    ctx.set_option("dp_max_cpl", 4)
+    try:
+        out = ctx.dp_packed(plots, want_sw=True)
+    finally:
+        ctx.set_option("dp_max_cpl", 16)
+    for b, B in enumerate(plots):
+        q, d = dp.qmax_dmax_serra09(B)
+        assert (out[b, 0], out[b, 1]) == (q, d)
+        assert pc.sw_close(out[b, 2], dp.sw_score(B))

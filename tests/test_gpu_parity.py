@@ -1,0 +1,100 @@
+"""GPU parity tests: the real libacoss_b200.so through its C ABI on a B200, against the golden
+vectors generated from the reference and against the oracle on seeded synthetic inputs."""
+import numpy as np
+import pytest
+
+import parity_checks as pc
+from acoss_b200 import _native, synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = _native.Context(0)  # raises if the CUDA library or the GPU is missing: no fallback
+    yield c
+    c.close()
+
+
+def test_golden_pairs(ctx, golden):
+    assert pc.check_golden_pairs(ctx, golden) >= 60
+
+
+def test_golden_dp(ctx, golden):
+    assert pc.check_golden_dp(ctx, golden) == 12
+
+
+def test_degenerate(ctx):
+    assert pc.check_degenerate(ctx) == 30
+
+
+def test_dense_tail(ctx):
+    assert pc.check_dense(ctx, [(20, 37), (45, 33), (5, 4), (300, 412), (700, 150), (1300, 90)]) == 6
+
+
+def test_covers80_shaped_sample_vs_oracle(ctx):
+    # covers80-shaped set (BASELINE configs[0]); a 60-pair sample keeps the oracle to ~20 s
+    songs, _ = synth.make_song_set("covers80", seed=80)
+    rng = np.random.default_rng(1)
+    pairs = rng.integers(0, len(songs), size=(60, 2)).astype(np.int32)
+    pairs = pairs[pairs[:, 0] != pairs[:, 1]]
+    n, tied = pc.check_against_oracle(ctx, songs, pairs, flags=_native.FLAG_NO_SWAP, want_sw=True)
+    assert tied <= 2
+    n2, _ = pc.check_against_oracle(ctx, songs, pairs[:20], flags=0, want_sw=False)
+
+
+def test_options_invariant(ctx):
+    songs, _ = synth.make_song_set("covers80", seed=22, n_songs=8, length_range=(120, 700))
+    pairs = np.array([(i, j) for i in range(8) for j in range(8) if i != j], np.int32)[:24]
+    pc.check_options_invariant(ctx, songs, pairs)
+
+
+def test_long_songs_vs_oracle(ctx):
+    # wide sweeps (several column groups), global-scratch ring, multi-block DP, m = 20
+    songs, _ = synth.make_song_set("covers80", seed=33, n_songs=4, length_range=(900, 2300))
+    pairs = np.array([(0, 1), (1, 0), (2, 3), (0, 3)], np.int32)
+    pc.check_against_oracle(ctx, songs, pairs, m=20, kappa=0.095, flags=_native.FLAG_NO_SWAP, want_sw=True)
+    pc.check_against_oracle(ctx, songs, pairs[:2], m=20, kappa=0.095, flags=0)
+
+
+def test_mfcc_path_no_oti(ctx):
+    # Serra09.py:177-184: 13 bins, no OTI / roll
+    rng = np.random.default_rng(13)
+    songs = []
+    for L in (180, 240, 310):
+        fr = rng.normal(size=(L, 13)).cumsum(axis=0).astype(np.float32) * 0.1 + rng.normal(size=(L, 13)).astype(np.float32)
+        songs.append({"chroma": np.ascontiguousarray(fr.T), "gchroma": None})
+    from oracle import crp_oracle, dp
+    ctx.upload_songs(songs)
+    pairs = np.array([(0, 1), (1, 2), (2, 0)], np.int32)
+    r = ctx.serra09_pairs(pairs, flags=_native.FLAG_NO_OTI | _native.FLAG_NO_SWAP, want_crp=True)
+    for p, (i, j) in enumerate(pairs):
+        _, B = crp_oracle.crp_pair(songs[i]["chroma"].astype(np.float64), songs[j]["chroma"].astype(np.float64),
+                                   None, None, 9, 0.095, do_oti=False)
+        assert np.array_equal(r["crp"][p], B)
+        assert (r["qmax_raw"][p], r["dmax_raw"][p]) == dp.qmax_dmax_serra09(B)
+
+
+def test_full_size_symmetry_property(ctx):
+    # whatisacover-shaped lengths (BASELINE configs[1]); no oracle at this size
+    songs, _ = synth.make_song_set("whatisacover", seed=10000, n_songs=400)
+    assert pc.check_symmetry(ctx, songs, n_pairs=2000) > 1500
+
+
+def test_float64_input(ctx):
+    songs, _ = synth.make_song_set("covers80", seed=5, n_songs=4, length_range=(100, 200))
+    rng = np.random.default_rng(0)
+    for s in songs:  # values that are NOT float32-representable (crema is float64)
+        s["chroma"] = s["chroma"].astype(np.float64) + rng.uniform(0, 1e-9, size=s["chroma"].shape)
+        s["gchroma"] = synth.global_chroma_f64(s["chroma"].T)
+    pairs = np.array([(0, 1), (2, 3), (1, 3)], np.int32)
+    pc.check_against_oracle(ctx, songs, pairs, flags=_native.FLAG_NO_SWAP)
+
+
+def test_errors(ctx):
+    songs, _ = synth.make_song_set("covers80", seed=5, n_songs=2, length_range=(50, 60))
+    ctx.upload_songs(songs)
+    with pytest.raises(_native.AcossError):
+        ctx.serra09_pairs(np.array([[0, 7]], np.int32))
+    with pytest.raises(_native.AcossError):
+        ctx.serra09_pairs(np.array([[0, 1]], np.int32), kappa=0.0)
