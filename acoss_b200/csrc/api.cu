@@ -18,6 +18,7 @@
 #include "kernels_dp.cuh"
 #include "kernels_prep.cuh"
 #include "kernels_sweep.cuh"
+#include "kernels_sweep2.cuh"
 
 #ifdef ACOSS_EMU
 #define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
@@ -139,12 +140,50 @@ namespace {
 
 constexpr int64_t kMaxChunkSepDoubles = (int64_t)1 << 28;  // 2 GiB
 constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
-constexpr int kCounterSlots = 16;
+constexpr int kCounterSlots = 32;
+constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) threads, up to 128 * (b + 1) columns
 
 struct ItemLists {
-    std::vector<uint32_t> thrA, thrB, crpA, crpB, dp4, dp8, dp16;
-    int thrB_w = 0, crpB_w = 0;
+    std::vector<uint32_t> fast0[kFastBuckets], fast2[kFastBuckets];  // fast sweep: separators / separators + CRP
+    std::vector<uint32_t> wide0, wide1;                              // general sweep (long songs): MODE 0 / MODE 1
+    std::vector<uint32_t> dp4, dp8, dp16;
+    int wide0_w = 0, wide1_w = 0;
 };
+
+template <int BINS, int MODE>
+int launch_sweep_fast(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter,
+                      uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    auto kfn = k_sweep_fast<BINS, MODE>;
+    const int T = 32 * (bucket + 1);
+    const int R = T / 32;
+    const size_t smem = fast_smem_bytes(T, m, R);
+    if (smem > (size_t)c->max_smem - 1024) return fail(ACOSS_ERR_ARG, "window m=%d too large for the fast sweep", m);
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, T, smem));
+    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep_fast cannot be resident (T %d, smem %zu B)", T, smem);
+    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
+    SweepArgs A;
+    memset(&A, 0, sizeof(A));
+    A.frames = c->frames.as<double>();
+    A.norms = c->norms.as<double>();
+    A.offs = c->offs.as<int64_t>();
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.counter = d_counter;
+    A.seps = c->seps.as<double>();
+    A.crp = c->crp.as<uint32_t>();
+    A.m = m;
+    A.R = R;
+    A.Wmax = 4 * T;
+    A.flags = flags;
+    ACOSS_LAUNCH(kfn, grid, T, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
 
 template <int BINS, int THREADS, int MODE>
 int launch_sweep(acoss_ctx* c, const uint32_t* d_items, int n_items, int Wmax, int m, unsigned int* d_counter,
@@ -280,24 +319,33 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         if (ok) {
             sep_total += (int64_t)w.M + w.N;
             crp_total += (int64_t)w.crp_rows * w.crp_wp;
-            // threshold sweeps: orientation 0 has song j on the columns, orientation 1 song i
-            const int wA = 128 * kSweepCPL, wB = 256 * kSweepCPL;
-            for (int o = 0; o < 2; ++o) {
-                if (o == 1 && nonmutual) break;
-                const int Lc = o ? w.Li : w.Lj;
-                if (Lc <= wA && !c->opt_force_wide) {
-                    L.thrA.push_back((uint32_t)p * 2 + o);
+            // Two sweeps per pair.  The CRP / DP orientation dpo has rows = the longer song; the
+            // other orientation supplies the separators of dpo's columns.
+            const int dpo = w.swap, other = 1 - dpo;
+            const int wB = 256 * kSweepCPL;
+            auto Lc_of = [&](int o) { return o ? w.Li : w.Lj; };
+            const bool fast_ok = !c->opt_force_wide && (size_t)fast_smem_bytes(256, m, 8) <= (size_t)c->max_smem - 1024;
+            if (!(nonmutual && dpo == 0)) {  // column separators of the CRP
+                const int Lc = Lc_of(other);
+                if (fast_ok && Lc <= kFastMaxCols) {
+                    L.fast0[(Lc - 1) / 128].push_back((uint32_t)p * 2 + other);
                 } else {
-                    L.thrB.push_back((uint32_t)p * 2 + o);
-                    L.thrB_w = std::max(L.thrB_w, (Lc + wB - 1) / wB * wB);
+                    L.wide0.push_back((uint32_t)p * 2 + other);
+                    L.wide0_w = std::max(L.wide0_w, (Lc + wB - 1) / wB * wB);
                 }
             }
-            const int Lc = w.swap ? w.Li : w.Lj;
-            if (Lc <= wA && !c->opt_force_wide) {
-                L.crpA.push_back((uint32_t)p);
-            } else {
-                L.crpB.push_back((uint32_t)p);
-                L.crpB_w = std::max(L.crpB_w, (Lc + wB - 1) / wB * wB);
+            {
+                const int Lc = Lc_of(dpo);
+                if (fast_ok && Lc <= kFastMaxCols) {
+                    L.fast2[(Lc - 1) / 128].push_back((uint32_t)p);
+                } else {
+                    if (!(nonmutual && dpo == 1)) {
+                        L.wide0.push_back((uint32_t)p * 2 + dpo);
+                        L.wide0_w = std::max(L.wide0_w, (Lc + wB - 1) / wB * wB);
+                    }
+                    L.wide1.push_back((uint32_t)p);
+                    L.wide1_w = std::max(L.wide1_w, (Lc + wB - 1) / wB * wB);
+                }
             }
         }
         classify_dp(c, L, (uint32_t)p, w.crp_cols);
@@ -312,25 +360,25 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     CU(c->swout.reserve((size_t)n * sizeof(float)));
     CU(c->otiout.reserve((size_t)n * sizeof(int32_t)));
     CU(c->counters.reserve(kCounterSlots * sizeof(unsigned int)));
-    const size_t n_items = L.thrA.size() + L.thrB.size() + L.crpA.size() + L.crpB.size() + L.dp4.size() +
-                           L.dp8.size() + L.dp16.size();
+    size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size();
+    for (int b = 0; b < kFastBuckets; ++b) n_items += L.fast0[b].size() + L.fast2[b].size();
     CU(c->items.reserve(std::max<size_t>(n_items, 1) * sizeof(uint32_t)));
     // stage: [PairWork...][items...]
     const size_t pw_bytes = (size_t)n * sizeof(PairWork);
     CU(c->h_stage.reserve(pw_bytes + n_items * sizeof(uint32_t) + 64));
     memcpy(c->h_stage.p, W.data(), pw_bytes);
     uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_stage.as<char>() + pw_bytes);
-    size_t o_thrA = 0, o_thrB, o_crpA, o_crpB, o_dp4, o_dp8, o_dp16, pos = 0;
+    size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16, pos = 0;
     auto put = [&](const std::vector<uint32_t>& v) {
         size_t at = pos;
         if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
         pos += v.size();
         return at;
     };
-    o_thrA = put(L.thrA);
-    o_thrB = put(L.thrB);
-    o_crpA = put(L.crpA);
-    o_crpB = put(L.crpB);
+    for (int b = 0; b < kFastBuckets; ++b) o_fast0[b] = put(L.fast0[b]);
+    for (int b = 0; b < kFastBuckets; ++b) o_fast2[b] = put(L.fast2[b]);
+    o_wide0 = put(L.wide0);
+    o_wide1 = put(L.wide1);
     o_dp4 = put(L.dp4);
     o_dp8 = put(L.dp8);
     o_dp16 = put(L.dp16);
@@ -353,12 +401,14 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     }
     CU(cudaEventRecord(c->ev[1], c->stream));
     int rc;
-    const int wA = 128 * kSweepCPL;
-    if ((rc = launch_sweep<BINS, 128, 0>(c, d_items + o_thrA, (int)L.thrA.size(), wA, m, d_cnt + 0, flags))) return rc;
-    if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_thrB, (int)L.thrB.size(), L.thrB_w, m, d_cnt + 1, flags))) return rc;
+    // largest buckets first: their CTAs are the long ones
+    for (int b = kFastBuckets - 1; b >= 0; --b)
+        if ((rc = launch_sweep_fast<BINS, 0>(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+    if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + 8, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
-    if ((rc = launch_sweep<BINS, 128, 1>(c, d_items + o_crpA, (int)L.crpA.size(), wA, m, d_cnt + 2, flags))) return rc;
-    if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_crpB, (int)L.crpB.size(), L.crpB_w, m, d_cnt + 3, flags))) return rc;
+    for (int b = kFastBuckets - 1; b >= 0; --b)
+        if ((rc = launch_sweep_fast<BINS, 2>(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + 9 + b, flags))) return rc;
+    if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 17, flags))) return rc;
     CU(cudaEventRecord(c->ev[3], c->stream));
     if ((rc = run_dp_lists(c, L, d_items, o_dp4, o_dp8, o_dp16, flags))) return rc;
     CU(cudaEventRecord(c->ev[4], c->stream));
