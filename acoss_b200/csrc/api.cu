@@ -154,9 +154,11 @@ template <int BINS, int MODE>
 int launch_sweep_fast(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter,
                       uint32_t flags) {
     if (n_items <= 0) return ACOSS_OK;
-    auto kfn = k_sweep_fast<BINS, MODE>;
+    // windows with a compiled-in specialisation: the reference default (Serra09.py:87) and the
+    // long-song stress configuration; anything else takes the runtime-m instantiation
+    auto kfn = (m == 9) ? k_sweep_fast<BINS, MODE, 9> : (m == 20 ? k_sweep_fast<BINS, MODE, 20> : k_sweep_fast<BINS, MODE, 0>);
     const int T = 32 * (bucket + 1);
-    const int R = T / 32;
+    const int R = std::min(T / 32, kFastMaxStripRows);
     const size_t smem = fast_smem_bytes(T, m, R);
     if (smem > (size_t)c->max_smem - 1024) return fail(ACOSS_ERR_ARG, "window m=%d too large for the fast sweep", m);
     CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -324,7 +326,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             const int dpo = w.swap, other = 1 - dpo;
             const int wB = 256 * kSweepCPL;
             auto Lc_of = [&](int o) { return o ? w.Li : w.Lj; };
-            const bool fast_ok = !c->opt_force_wide && (size_t)fast_smem_bytes(256, m, 8) <= (size_t)c->max_smem - 1024;
+            const bool fast_ok = !c->opt_force_wide && (size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows) <= (size_t)c->max_smem - 1024;
             if (!(nonmutual && dpo == 0)) {  // column separators of the CRP
                 const int Lc = Lc_of(other);
                 if (fast_ok && Lc <= kFastMaxCols) {
@@ -404,11 +406,11 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     // largest buckets first: their CTAs are the long ones
     for (int b = kFastBuckets - 1; b >= 0; --b)
         if ((rc = launch_sweep_fast<BINS, 0>(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
-    if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + 8, flags))) return rc;
+    if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
     for (int b = kFastBuckets - 1; b >= 0; --b)
-        if ((rc = launch_sweep_fast<BINS, 2>(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + 9 + b, flags))) return rc;
-    if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 17, flags))) return rc;
+        if ((rc = launch_sweep_fast<BINS, 2>(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
+    if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
     CU(cudaEventRecord(c->ev[3], c->stream));
     if ((rc = run_dp_lists(c, L, d_items, o_dp4, o_dp8, o_dp16, flags))) return rc;
     CU(cudaEventRecord(c->ev[4], c->stream));

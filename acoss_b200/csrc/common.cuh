@@ -63,9 +63,7 @@ __device__ __forceinline__ double warp_min(double v) {
     return v;
 }
 __device__ __forceinline__ int warp_sum(int v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
-    return v;
+    return __reduce_add_sync(kFullMask, v);  // REDUX.SUM: one instruction instead of five shuffles
 }
 
 }  // namespace acoss

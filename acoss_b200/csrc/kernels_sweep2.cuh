@@ -31,7 +31,8 @@
 namespace acoss {
 
 constexpr int kFastXS = 14;       // staged row: 12/13 bins (+ pad), [XS-1] = windowed norm sum
-constexpr int kFastMaxCols = 1024;
+constexpr int kFastMaxCols = 1408;  // 352 threads x 4 columns: 352 x 168 registers still fit one SM
+constexpr int kFastMaxStripRows = 8;
 
 __host__ __device__ inline int fast_padt(int m) { return (m + 3) / 4 + 1; }
 
@@ -51,10 +52,17 @@ struct SelState {
     int have;
 };
 
-// count of strip-row values <= t (invalid positions hold +inf)
+// count of strip-row values <= t (invalid positions hold +inf); n4 is a multiple of 128
 __device__ __forceinline__ int strip_count(const double* row, int n4, double t, int lane) {
     int c = 0;
-    for (int p = lane; p < n4; p += 32) c += (row[p] <= t) ? 1 : 0;
+    const double* q = row + lane;
+    for (int p = 0; p < n4; p += 128, q += 128) {
+        const double v0 = q[0], v1 = q[32], v2 = q[64], v3 = q[96];
+        c += (v0 <= t) ? 1 : 0;
+        c += (v1 <= t) ? 1 : 0;
+        c += (v2 <= t) ? 1 : 0;
+        c += (v3 <= t) ? 1 : 0;
+    }
     return warp_sum(c);
 }
 
@@ -137,7 +145,10 @@ __device__ inline bool strip_select(const double* row, int n4, int k, double g, 
     return found;
 }
 
-template <int BINS, int MODE>
+
+// MW > 0: the embedding window m is a compile-time constant (every ring offset becomes an
+// immediate or one add); MW == 0: m is read from the arguments (any window, slower addressing).
+template <int BINS, int MODE, int MW>
 __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
     constexpr int CPL = 4;
     constexpr int XS = kFastXS;
@@ -147,28 +158,28 @@ __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
 
     const int T = (int)blockDim.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
-    const int m = A.m, RD = m + 1, R = A.R;
+    const int m = (MW > 0) ? MW : A.m;
+    const int RD = m + 1, R = A.R;
     const int PADT = fast_padt(m), TWP = T + PADT, RS = 4 * TWP, SS = 4 * T;
 
-    double* ring = reinterpret_cast<double*>(smem_raw);
-    double* strip = ring + (size_t)RD * RS;
-    double* xs = strip + (size_t)R * SS;
-    double* rsz = xs + kStageRows * XS;  // [R] row separators (relative units) of the strip
-    double* wxs = rsz + R;               // [R] windowed row norms of the strip rows
-    uint32_t* bitrows = reinterpret_cast<uint32_t*>(wxs + R);
+    double* const ring = reinterpret_cast<double*>(smem_raw);
+    double* const strip = ring + RD * RS;
+    double* const xs = strip + R * SS;
+    double* const rsz = xs + kStageRows * XS;  // [R] row separators (relative units) of the strip
+    double* const wxs = rsz + R;               // [R] windowed row norms of the strip rows
+    uint32_t* const bitrows = reinterpret_cast<uint32_t*>(wxs + R);
     const int BW = T / 8 + 2;
 
-    // per-thread constant positions inside a ring row (doubles)
-    int own[CPL], pooff[CPL];
+    // Column 4*tid + r of a ring row sits at ring_t[r * TWP]; the cell m columns to the left at
+    // ring_t[pooff(r)]; the left neighbour of column 4*tid at ring_t[3 * TWP - 1].
+    double* const ring_t = ring + tid + PADT;
+    int pooff[CPL];
 #pragma unroll
     for (int r = 0; r < CPL; ++r) {
-        own[r] = r * TWP + tid + PADT;
-        const int d = r - m;                      // column 4*tid + r - m
+        const int d = r - m;
         const int q = (d >= 0) ? (d >> 2) : -((-d + 3) >> 2);
-        const int rp = d - 4 * q;
-        pooff[r] = rp * TWP + tid + q + PADT;
+        pooff[r] = q + (d - 4 * q) * TWP;
     }
-    const int pdoff = 3 * TWP + tid - 1 + PADT;  // column 4*tid - 1
 
     for (;;) {
         if (tid == 0) s_item = (int)atomicAdd(A.counter, 1u);
@@ -265,33 +276,34 @@ __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
             const double* xr = xs + (a & (kStageRows - 1)) * XS;
             double x[BINS];
 #pragma unroll
-            for (int k = 0; k < BINS; ++k) x[k] = xr[k];
+            for (int k = 0; k + 1 < BINS; k += 2) {
+                const double2 v = *reinterpret_cast<const double2*>(xr + k);
+                x[k] = v.x;
+                x[k + 1] = v.y;
+            }
+            if (BINS & 1) x[BINS - 1] = xr[BINS - 1];
             const int i = a - (m - 1);
 
-            const double* ring1 = ring + slot1 * RS;
-            const double* ringm = ring + slotm * RS;
-            double* ring0 = ring + slot0 * RS;
-            double P[CPL], z[CPL];
+            const double* r1 = ring_t + slot1 * RS;
+            const double* rm = ring_t + slotm * RS;
+            double* r0 = ring_t + slot0 * RS;
+            double P[CPL];
 #pragma unroll
             for (int r = 0; r < CPL; ++r) {
-                double acc = (r == 0) ? ring1[pdoff] : Pprev[r - 1];
+                double acc = (r == 0) ? r1[3 * TWP - 1] : Pprev[r - 1];
 #pragma unroll
                 for (int k = 0; k < BINS; ++k) acc = fma(x[k], y2[r][k], acc);
                 P[r] = acc;
             }
+            double* srow = strip + si * SS + tid;
 #pragma unroll
             for (int r = 0; r < CPL; ++r) {
-                z[r] = (P[r] - ringm[pooff[r]]) + wy[r];
-                ring0[own[r]] = P[r];
+                const double z = (P[r] - rm[pooff[r]]) + wy[r];
+                r0[r * TWP] = P[r];
                 Pprev[r] = P[r];
+                if (i >= 0 && (vmask & (1u << r))) srow[r * T] = z;
             }
-            if (i >= 0) {
-                double* srow = strip + si * SS + tid;
-#pragma unroll
-                for (int r = 0; r < CPL; ++r)
-                    if (vmask & (1u << r)) srow[r * T] = z[r];
-                if (tid == 0) wxs[si] = xr[XS - 1];
-            }
+            if (i >= 0 && tid == 0) wxs[si] = xr[XS - 1];
             __syncthreads();
             slot1 = slot0;
             slot0 = (slot0 + 1 == RD) ? 0 : slot0 + 1;
@@ -303,13 +315,15 @@ __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
                     const int i0 = i - si;
                     // ---- selection: one warp per strip row
                     for (int rr = warp; rr < nrows; rr += NW) {
-                        const double* srow = strip + rr * SS;
+                        const double* sel = strip + rr * SS;
                         const double wxr = wxs[rr];
                         double t = INF;
                         if (kk <= 0) {
                             t = -INF;
                         } else if (kk < No && (MODE == 0 || use_row)) {
-                            strip_select(srow, SS, kk, st.guess - wxr, st, lane, t);
+                            const double g = st.guess - wxr;
+                            st.have = st.have && (g > -INF) && (g < INF);
+                            strip_select(sel, SS, kk, g, st, lane, t);
                             st.guess = t + wxr;
                             st.have = 1;
                             if (MODE == 0) {
@@ -317,7 +331,7 @@ __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
                                 // other orientation's differently rounded distances
                                 double vk = -INF, vk1 = INF;
                                 for (int p = lane; p < SS; p += 32) {
-                                    const double v = srow[p];
+                                    const double v = sel[p];
                                     if (v <= t)
                                         vk = fmax(vk, v);
                                     else
@@ -341,11 +355,11 @@ __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
                         // ---- strip -> packed bits (column space), then shifted copy-out
                         for (int rr = 0; rr < nrows; ++rr) {
                             const double rz = rsz[rr], wxr = wxs[rr];
-                            const double* srow = strip + rr * SS + tid;
+                            const double* own = strip + rr * SS + tid;
                             unsigned nib = 0;
 #pragma unroll
                             for (int r = 0; r < CPL; ++r) {
-                                const double v = srow[r * T];
+                                const double v = own[r * T];
                                 nib |= ((v <= rz) && ((v + wxr) <= cs[r])) ? (1u << r) : 0u;
                             }
                             unsigned w = nib << (4 * (lane & 7));
@@ -354,8 +368,6 @@ __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
                             w |= __shfl_xor_sync(kFullMask, w, 4);
                             if ((lane & 7) == 0) bitrows[rr * BW + (tid >> 3)] = w;
                         }
-                        // restore +inf so that stale values of this strip never leak into a
-                        // shorter last strip
                         __syncthreads();
                         const int wp = pw.crp_wp;
                         const unsigned sh = (unsigned)(m - 1) & 31u;
