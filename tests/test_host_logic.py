@@ -1,0 +1,168 @@
+"""CPU-only tests of the host side: C-ABI surface, HDF5 io, the plugin mirror's pair enumeration,
+batch blocks, evaluation statistics and feature aggregation."""
+import itertools
+import os
+import re
+
+import numpy as np
+import pytest
+
+from acoss_b200 import _native, hdf5io, synth
+from acoss_b200.cover_algorithm import CoverAlgorithm
+from acoss_b200.serra09 import Serra09, global_chroma, sync_aggregate
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "acoss_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(acoss_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_abi_exports_every_declared_symbol():
+    if not os.path.exists(_native.DEFAULT_LIB):
+        from acoss_b200 import build
+        build.build()
+    lib = _native.load_library()  # binds every name in SIGNATURES or raises
+    names = declared_symbols()
+    assert len(names) >= 16
+    for n in names:
+        assert hasattr(lib, n), n
+        assert n in _native.SIGNATURES, "binding missing for %s" % n
+    assert sorted(_native.SIGNATURES) == names
+    assert lib.acoss_version() >= 100
+
+
+def test_no_gpu_means_loud_failure_not_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(_native.AcossError):
+        _native.Context(0)
+
+
+def test_hdf5_roundtrip(tmp_path):
+    d = {"chroma_qmax": np.random.rand(7, 7).astype(np.float32),
+         "similarities": {"idxs": np.arange(10).reshape(5, 2), "chroma_dmax": np.random.rand(5),
+                          "empty": np.zeros((0, 2), np.int64)},
+         "label": "clique_1", "n": 3, "f": 2.5, "flag": True, "nothing": None,
+         "hpcp": np.random.rand(20, 12).astype(np.float32), "u8": np.arange(5, dtype=np.uint8)}
+    p = str(tmp_path / "t.h5")
+    hdf5io.save(p, d)
+    r = hdf5io.load(p)
+    assert sorted(r) == sorted(d)
+    for k in ("chroma_qmax", "hpcp", "u8"):
+        assert r[k].dtype == d[k].dtype and np.array_equal(r[k], d[k])
+    assert np.array_equal(r["similarities"]["idxs"], d["similarities"]["idxs"])
+    assert r["similarities"]["empty"].shape == (0, 2)
+    assert (r["label"], r["n"], r["f"], r["nothing"]) == ("clique_1", 3, 2.5, None)
+    # many entries in one group, and the file starts with the HDF5 signature + superblock v0
+    big = {"k%03d" % i: np.full(3, i) for i in range(150)}
+    hdf5io.save(p, big)
+    r = hdf5io.load(p)
+    assert len(r) == 150 and r["k042"][0] == 42
+    raw = open(p, "rb").read(16)
+    assert raw[:8] == b"\x89HDF\r\n\x1a\n" and raw[8] == 0
+
+
+def test_all_pairs_order_matches_itertools():
+    songs, labels = synth.make_song_set("covers80", seed=1, n_songs=7, length_range=(20, 30))
+    alg = CoverAlgorithm(songs=songs, labels=labels, do_memmaps=False)
+    assert [tuple(p) for p in alg.all_pairs_list(True)] == list(itertools.combinations(range(7), 2))
+    assert [tuple(p) for p in alg.all_pairs_list(False)] == list(itertools.permutations(range(7), 2))
+
+
+def test_batch_blocks_cover_lower_triangle():
+    # runcovers80.sh: w = 20 over 160 songs -> 36 blocks (CoverAlgorithm.py:227-244)
+    songs = [{"chroma": np.zeros((12, 1), np.float32), "gchroma": np.ones(12)} for _ in range(40)]
+    alg = CoverAlgorithm(songs=songs, labels=["x"] * 40, do_memmaps=False)
+    w, wsub = 10, 5
+    seen = set()
+    nblocks = (40 // w) * (40 // w + 1) // 2
+    for idx in range(nblocks):
+        for i in range(w // wsub):
+            for j in range(w // wsub):
+                for a, b in alg.batch_block_idxs(w, idx, wsub, i, j):
+                    assert a >= b
+                    assert (a, b) not in seen
+                    seen.add((int(a), int(b)))
+    assert seen == {(a, b) for a in range(40) for b in range(a + 1)}
+
+
+def reference_eval(D, cliques):
+    """Direct restatement of the rank loop of CoverAlgorithm.py:345-395 (the O(N^2) version)."""
+    from itertools import chain
+    N = D.shape[0]
+    cl = [list(c) for c in cliques]
+    Ks = np.array([len(c) for c in cl])
+    idx = np.argsort(-Ks, kind="stable")
+    Ks = Ks[idx]
+    cl = [cl[i] for i in idx]
+    idx = np.array(list(chain(*cl)), dtype=int)
+    D = D[idx, :][:, idx].copy()
+    np.fill_diagonal(D, -np.inf)
+    order = np.argsort(-D, 1)
+    ranks = np.nan * np.ones(N)
+    AllMap = np.nan * np.ones(N)
+    startidx, kidx = 0, 0
+    for i in range(N):
+        if i >= startidx + Ks[kidx]:
+            startidx += Ks[kidx]
+            kidx += 1
+            if Ks[kidx] < 2:
+                break
+        iranks = [k + 1 for k in range(N) if 0 <= order[i, k] - startidx < Ks[kidx]][0:-1]
+        ranks[i] = iranks[0]
+        AllMap[i] = np.mean([float(j) / float(r) for j, r in zip(range(1, Ks[kidx]), iranks)])
+    ranks = ranks[~np.isnan(ranks)]
+    return np.mean(ranks), np.sum(1.0 / ranks) / N, np.median(ranks), np.nanmean(AllMap)
+
+
+def test_eval_statistics_match_reference_loop(tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+    rng = np.random.default_rng(3)
+    labels = ["a"] * 3 + ["b"] * 2 + ["c"] * 2 + ["d", "e", "f"]
+    perm = rng.permutation(len(labels))
+    labels = [labels[p] for p in perm]
+    n = len(labels)
+    songs = [{"chroma": np.zeros((12, 1), np.float32), "gchroma": np.ones(12), "label": labels[i]} for i in range(n)]
+    alg = CoverAlgorithm(songs=songs, labels=labels, similarity_types=["main"], do_memmaps=False, cachedir=str(tmp_path))
+    D = rng.uniform(size=(n, n)).astype(np.float32)
+    D = D + D.T
+    alg.Ds["main"] = D
+    alg.get_all_clique_ids()
+    MR, MRR, MDR, MAP, tops = alg.getEvalStatistics("main", topsidx=[1, 3])
+    ref = reference_eval(D, list(alg.cliques.values()))
+    assert np.allclose([MR, MRR, MDR, MAP], ref)
+    assert os.path.exists("results_full.csv")
+    assert open("results_full.csv").readline().startswith("name, MR, MRR, MDR, MAP,Top-1")
+
+
+def test_feature_aggregation_matches_definition():
+    rng = np.random.default_rng(0)
+    chroma = rng.uniform(size=(95, 12)).astype(np.float32)   # (n_frames, 12) like hpcp
+    g = global_chroma(chroma)
+    assert g.shape == (12,) and g.max() == 1.0
+    agg = sync_aggregate(chroma.T, 40, np.median)
+    assert agg.shape == (12, 3)
+    assert np.array_equal(agg[:, 0], np.median(chroma[:40].T, axis=1))
+    assert np.array_equal(agg[:, 2], np.median(chroma[80:].T, axis=1))
+    with pytest.raises(IOError):
+        global_chroma(np.zeros((5, 13)))
+
+
+def test_serra09_load_features_from_files(tmp_path):
+    # per-song .h5 with the fields extractors.py writes (hpcp, mfcc_htk, label)
+    rng = np.random.default_rng(1)
+    for s in range(3):
+        hdf5io.save(str(tmp_path / ("song%d.h5" % s)),
+                    {"hpcp": rng.uniform(size=(400 + 37 * s, 12)).astype(np.float32),
+                     "mfcc_htk": rng.normal(size=(13, 400 + 37 * s)).astype(np.float32),
+                     "label": "c%d" % (s % 2), "track_id": "t%d" % s})
+    alg = Serra09(datapath=str(tmp_path), chroma_type="hpcp", shortname="t", do_memmaps=False)
+    assert alg.N == 3
+    f = alg.load_features(2)
+    L = int(np.ceil((400 + 74) / 40))
+    assert f["chroma"].shape == (12, L) and f["mfcc"].shape == (13, L) and f["gchroma"].shape == (12,)
+    assert alg.cliques == {"c0": {2}}
