@@ -127,8 +127,10 @@ struct acoss_ctx {
     // test/tuning knobs (acoss_set_option)
     int opt_force_wide = 0;      // send every sweep item through the 256-thread kernels
     int opt_force_gscratch = 0;  // ring + strip in global scratch even when shared memory would do
-    int opt_dp_max_cpl = 16;     // widest DP kernel allowed (4, 8, 16): narrower forces column blocks
+    int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
+                                 // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
     int opt_chunk_pairs = 1 << 18;
+    uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
     // accounting
     int64_t launches = 0;
     float stage_ms[5] = {0, 0, 0, 0, 0};
@@ -575,6 +577,7 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
     }
     for (int s = 0; s < 5; ++s) c->stage_ms[s] = 0.f;
     c->have_stage_ms = true;
+    flags |= c->opt_debug_flags;
     int64_t p0 = 0;
     while (p0 < P) {
         // cut a chunk whose scratch fits the budget
@@ -828,6 +831,8 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
         c->opt_force_wide = value != 0;
     else if (n == "force_gscratch")
         c->opt_force_gscratch = value != 0;
+    else if (n == "debug_flags")
+        c->opt_debug_flags = (uint32_t)value;
     else if (n == "dp_max_cpl") {
         if (value != 4 && value != 8 && value != 16) return fail(ACOSS_ERR_ARG, "dp_max_cpl must be 4, 8 or 16");
         c->opt_dp_max_cpl = (int)value;

@@ -320,6 +320,8 @@ __global__ void ACOSS_MAXNREG(168) k_sweep_fast(SweepArgs A) {
                         double t = INF;
                         if (kk <= 0) {
                             t = -INF;
+                        } else if (A.flags & (1u << 30)) {
+                            t = 1.0;  // profiling knob: skip the selection (results are meaningless)
                         } else if (kk < No && (MODE == 0 || use_row)) {
                             const double g = st.guess - wxr;
                             st.have = st.have && (g > -INF) && (g < INF);

@@ -310,6 +310,15 @@ inline int __reduce_add_sync(unsigned, int v) {
     emu::warp_barrier();
     return r;
 }
+inline int __reduce_max_sync(unsigned, int v) {
+    emu::Warp& w = emu::my_warp();
+    w.slot[emu::lane_id()] = (uint64_t)(uint32_t)v;
+    emu::warp_barrier();
+    int r = (int)(uint32_t)w.slot[0];
+    for (int l = 1; l < 32; ++l) r = std::max(r, (int)(uint32_t)w.slot[l]);
+    emu::warp_barrier();
+    return r;
+}
 inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }
 inline int __all_sync(unsigned m, int pred) { return __ballot_sync(m, pred) == 0xffffffffu; }
 

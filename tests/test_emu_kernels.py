@@ -60,7 +60,7 @@ def test_emu_dp_multiblock(ctx):
     try:
         out = ctx.dp_packed(plots, want_sw=True)
     finally:
-        ctx.set_option("dp_max_cpl", 16)
+        ctx.set_option("dp_max_cpl", 4)
     for b, B in enumerate(plots):
         q, d = dp.qmax_dmax_serra09(B)
         assert (out[b, 0], out[b, 1]) == (q, d)
