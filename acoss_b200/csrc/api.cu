@@ -19,6 +19,7 @@
 #include "kernels_prep.cuh"
 #include "kernels_sweep.cuh"
 #include "kernels_sweep2.cuh"
+#include "kernels_sweep3.cuh"
 
 #ifdef ACOSS_EMU
 #define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
@@ -130,6 +131,8 @@ struct acoss_ctx {
     int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
                                  // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
     int opt_chunk_pairs = 1 << 18;
+    int opt_sweep_gen = 2;         // 2: phase-alternating sweep (kernels_sweep2.cuh, measured fastest so far);
+                                   // 3: warp-specialised sweep (kernels_sweep3.cuh, 15 % slower: profiles/exp)
     uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
     // accounting
     int64_t launches = 0;
@@ -184,6 +187,42 @@ int launch_sweep_fast(acoss_ctx* c, const uint32_t* d_items, int n_items, int bu
     A.Wmax = 4 * T;
     A.flags = flags;
     ACOSS_LAUNCH(kfn, grid, T, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
+template <int BINS, int MODE>
+int launch_sweep_ws(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter,
+                    uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    auto kfn = (m == 9) ? k_sweep_ws<BINS, MODE, 9> : (m == 20 ? k_sweep_ws<BINS, MODE, 20> : k_sweep_ws<BINS, MODE, 0>);
+    const int TC = 32 * (bucket + 1);
+    const int NS = ws_sel_warps(TC);
+    const int TT = TC + 32 * NS;
+    const size_t smem = ws_smem_bytes(TC, m);
+    if (smem > (size_t)c->max_smem - 1024) return fail(ACOSS_ERR_ARG, "window m=%d too large for the fast sweep", m);
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, TT, smem));
+    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep_ws cannot be resident (threads %d, smem %zu B)", TT, smem);
+    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
+    SweepArgs A;
+    memset(&A, 0, sizeof(A));
+    A.frames = c->frames.as<double>();
+    A.norms = c->norms.as<double>();
+    A.offs = c->offs.as<int64_t>();
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.counter = d_counter;
+    A.seps = c->seps.as<double>();
+    A.crp = c->crp.as<uint32_t>();
+    A.m = m;
+    A.R = 2 * NS;
+    A.Wmax = 4 * TC;
+    A.flags = flags;
+    ACOSS_LAUNCH(kfn, grid, TT, smem, c->stream, A);
     c->launches++;
     CU(cudaGetLastError());
     return ACOSS_OK;
@@ -328,7 +367,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             const int dpo = w.swap, other = 1 - dpo;
             const int wB = 256 * kSweepCPL;
             auto Lc_of = [&](int o) { return o ? w.Li : w.Lj; };
-            const bool fast_ok = !c->opt_force_wide && (size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows) <= (size_t)c->max_smem - 1024;
+            const bool fast_ok = !c->opt_force_wide && std::max((size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows), (size_t)ws_smem_bytes(32 * kFastBuckets, m)) <= (size_t)c->max_smem - 1024;
             if (!(nonmutual && dpo == 0)) {  // column separators of the CRP
                 const int Lc = Lc_of(other);
                 if (fast_ok && Lc <= kFastMaxCols) {
@@ -407,11 +446,11 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     int rc;
     // largest buckets first: their CTAs are the long ones
     for (int b = kFastBuckets - 1; b >= 0; --b)
-        if ((rc = launch_sweep_fast<BINS, 0>(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+        if ((rc = (c->opt_sweep_gen == 2 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
     if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
     for (int b = kFastBuckets - 1; b >= 0; --b)
-        if ((rc = launch_sweep_fast<BINS, 2>(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
+        if ((rc = (c->opt_sweep_gen == 2 ? launch_sweep_fast<BINS, 2> : launch_sweep_ws<BINS, 2>)(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
     if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
     CU(cudaEventRecord(c->ev[3], c->stream));
     if ((rc = run_dp_lists(c, L, d_items, o_dp4, o_dp8, o_dp16, flags))) return rc;
@@ -831,7 +870,10 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
         c->opt_force_wide = value != 0;
     else if (n == "force_gscratch")
         c->opt_force_gscratch = value != 0;
-    else if (n == "debug_flags")
+    else if (n == "sweep_gen") {
+        if (value != 2 && value != 3) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2 or 3");
+        c->opt_sweep_gen = (int)value;
+    } else if (n == "debug_flags")
         c->opt_debug_flags = (uint32_t)value;
     else if (n == "dp_max_cpl") {
         if (value != 4 && value != 8 && value != 16) return fail(ACOSS_ERR_ARG, "dp_max_cpl must be 4, 8 or 16");

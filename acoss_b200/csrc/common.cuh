@@ -48,6 +48,23 @@ struct PairWork {
     int64_t bnd_off;         // into the DP boundary scratch (int4 records), -1 when unused
 };
 
+// Named barriers (PTX bar.sync / bar.arrive with an explicit thread count): the producer /
+// consumer hand-over between the compute warps and the selection warps of the sweep kernel.
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+#ifdef ACOSS_EMU
+    emu::bar_named(id, count, true);
+#else
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+#endif
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int count) {
+#ifdef ACOSS_EMU
+    emu::bar_named(id, count, false);
+#else
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+#endif
+}
+
 __device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
 __device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
 __device__ __forceinline__ int imax3(int a, int b, int c) { return imax(imax(a, b), c); }

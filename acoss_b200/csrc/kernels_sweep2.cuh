@@ -85,11 +85,11 @@ __device__ inline bool strip_select(const double* row, int n4, int k, double g, 
                 if (c < k) {
                     lo = t; clo = c; have_lo = true;
                     if (have_hi) break;
-                    t = lo + step * (1.5 * (double)(k - c));
+                    t = fma(step, (double)(1.5f * (float)(k - c)), lo);
                 } else {
                     hi = t; chi = c; have_hi = true;
                     if (have_lo) break;
-                    t = hi - step * (1.5 * (double)(c - k));
+                    t = fma(-step, (double)(1.5f * (float)(c - k)), hi);
                 }
                 step *= 2.0;
                 c = strip_count(row, n4, t, lane);
@@ -124,7 +124,7 @@ __device__ inline bool strip_select(const double* row, int n4, int k, double g, 
             if (iter & 1)
                 t = 0.5 * lo + 0.5 * hi;
             else
-                t = lo + (hi - lo) * ((double)(k - clo) / (double)(chi - clo));
+                t = fma(hi - lo, (double)__fdividef((float)(k - clo), (float)(chi - clo)), lo);  // fp32 ratio: no DDIV
             if (!(t > lo && t < hi)) {
                 t = 0.5 * lo + 0.5 * hi;
                 if (!(t > lo && t < hi)) break;
@@ -138,7 +138,7 @@ __device__ inline bool strip_select(const double* row, int n4, int k, double g, 
                 hi = t; chi = c;
             }
         }
-        if (chi > clo && hi > lo && hi < INF && lo > -INF) st.spacing = (hi - lo) / (double)(chi - clo);
+        if (chi > clo && hi > lo && hi < INF && lo > -INF) st.spacing = (hi - lo) * (double)__fdividef(1.0f, (float)(chi - clo));
     }
     if (!found) t = lo;
     t_out = t;

@@ -63,6 +63,8 @@ struct Block {
     int nthreads = 0;
     int bar_arrived = 0;
     unsigned bar_gen = 0;
+    int named_arrived[16] = {0};
+    unsigned named_gen[16] = {0};
     std::vector<Warp> warps;
 };
 
@@ -71,7 +73,8 @@ struct Fiber {
     char* stack = nullptr;
     bool done = false;
     bool block_wait = false;
-    unsigned block_wait_gen = 0;
+    const unsigned* wait_ptr = nullptr;  // parked while *wait_ptr == wait_val
+    unsigned wait_val = 0;
     uint3 tid;
     int linear = 0;
 };
@@ -137,6 +140,7 @@ inline void launch(dim3 grid, dim3 block, size_t smem, const std::function<void(
                 s.blk.nthreads = nthreads;
                 s.blk.bar_arrived = 0;
                 s.blk.bar_gen = 0;
+                for (int nb = 0; nb < 16; ++nb) s.blk.named_arrived[nb] = 0, s.blk.named_gen[nb] = 0;
                 s.blk.warps.assign(nwarps, Warp());
                 for (int t = 0; t < nthreads; ++t) {
                     Fiber& f = s.fibers[t];
@@ -164,7 +168,7 @@ inline void launch(dim3 grid, dim3 block, size_t smem, const std::function<void(
                             for (int l = 0; l < 32; ++l) {
                                 Fiber& f = s.fibers[w * 32 + l];
                                 if (f.done) continue;
-                                if (f.block_wait && f.block_wait_gen == s.blk.bar_gen) continue;
+                                if (f.block_wait && *f.wait_ptr == f.wait_val) continue;
                                 f.block_wait = false;
                                 s.cur = &f;
                                 swapcontext(&s.main_ctx, &f.ctx);
@@ -203,7 +207,28 @@ inline void syncthreads() {
     }
     while (s.blk.bar_gen == gen) {
         f->block_wait = true;
-        f->block_wait_gen = gen;
+        f->wait_ptr = &s.blk.bar_gen;
+        f->wait_val = gen;
+        yield_();
+    }
+    f->block_wait = false;
+}
+
+// PTX bar.sync id, count / bar.arrive id, count (named barriers 1..15)
+inline void bar_named(int id, int count, bool wait) {
+    State& s = st();
+    Fiber* f = s.cur;
+    unsigned gen = s.blk.named_gen[id];
+    if (++s.blk.named_arrived[id] == count) {
+        s.blk.named_arrived[id] = 0;
+        s.blk.named_gen[id]++;
+        return;
+    }
+    if (!wait) return;
+    while (s.blk.named_gen[id] == gen) {
+        f->block_wait = true;
+        f->wait_ptr = &s.blk.named_gen[id];
+        f->wait_val = gen;
         yield_();
     }
     f->block_wait = false;
@@ -343,6 +368,7 @@ inline double __fma_rn(double a, double b, double c) { return std::fma(a, b, c);
 inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
 inline float __fadd_rn(float a, float b) { volatile float r = a + b; return r; }
 inline float __fmul_rn(float a, float b) { volatile float r = a * b; return r; }
+inline float __fdividef(float a, float b) { return a / b; }
 inline int __double2int_rn(double v) { return (int)std::nearbyint(v); }
 inline double __longlong_as_double(long long v) { return emu::from_bits<double>((uint64_t)v); }
 inline long long __double_as_longlong(double v) { return (long long)emu::to_bits(v); }
