@@ -20,6 +20,7 @@
 #include "kernels_sweep.cuh"
 #include "kernels_sweep2.cuh"
 #include "kernels_sweep3.cuh"
+#include "kernels_sweep4.cuh"
 
 #ifdef ACOSS_EMU
 #define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
@@ -123,6 +124,8 @@ struct acoss_ctx {
     // per-chunk scratch
     DevBuf pairs, items, counters, seps, crp, bnd, qout, dout, swout, otiout, gscratch;
     DevBuf dense_in, dense_desc, dense_starts;
+    DevBuf lens, wnorm, wnmax, sepk, sepx, nb;  // gen-4 sweep: windowed norms, integer separators, nibble CRPs
+    int wnorm_m = -1;                           // window the wnorm buffer was computed for
     PinBuf h_stage;
     std::vector<uint32_t> h_crp;
     // test/tuning knobs (acoss_set_option)
@@ -131,8 +134,9 @@ struct acoss_ctx {
     int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
                                  // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
     int opt_chunk_pairs = 1 << 18;
-    int opt_sweep_gen = 2;         // 2: phase-alternating sweep (kernels_sweep2.cuh, measured fastest so far);
-                                   // 3: warp-specialised sweep (kernels_sweep3.cuh, 15 % slower: profiles/exp)
+    int opt_sweep_gen = 4;         // 4: integer-key sweep (kernels_sweep4.cuh, default); 2: float64-selection sweep
+                                   // (kernels_sweep2.cuh); 3: warp-specialised variant of 2 (kernels_sweep3.cuh)
+    int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
     uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
     // accounting
     int64_t launches = 0;
@@ -145,15 +149,62 @@ namespace {
 
 constexpr int64_t kMaxChunkSepDoubles = (int64_t)1 << 28;  // 2 GiB
 constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
-constexpr int kCounterSlots = 32;
+constexpr int64_t kMaxChunkNbBytes = (int64_t)6 << 30;     // 6 GiB of nibble-byte CRPs (gen 4)
+constexpr int kCounterSlots = 64;
 constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) threads, up to 128 * (b + 1) columns
 
 struct ItemLists {
     std::vector<uint32_t> fast0[kFastBuckets], fast2[kFastBuckets];  // fast sweep: separators / separators + CRP
     std::vector<uint32_t> wide0, wide1;                              // general sweep (long songs): MODE 0 / MODE 1
+    std::vector<uint32_t> g4_0[kFastBuckets], g4_2[kFastBuckets];    // gen-4 sweep: separators / CRP
+    std::vector<uint32_t> g4_pack;                                   // pairs whose nibble CRP needs packing
     std::vector<uint32_t> dp4, dp8, dp16;
     int wide0_w = 0, wide1_w = 0;
 };
+
+template <int BINS, int MODE>
+int launch_sweep4(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter,
+                  uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    const int T = 32 * (bucket + 1);
+    auto kfn = k_sweep4<BINS, MODE, 0, 0>;
+    if (m == 9) {
+        switch (bucket + 1) {  // register-resident keys for CTAs of up to 5 warps
+            case 1: kfn = k_sweep4<BINS, MODE, 9, 1>; break;
+            case 2: kfn = k_sweep4<BINS, MODE, 9, 2>; break;
+            case 3: kfn = k_sweep4<BINS, MODE, 9, 3>; break;
+            case 4: kfn = k_sweep4<BINS, MODE, 9, 4>; break;
+            case 5: kfn = k_sweep4<BINS, MODE, 9, 5>; break;
+            default: kfn = k_sweep4<BINS, MODE, 9, 0>; break;
+        }
+    }
+    const size_t smem = (size_t)s4_layout(T, m, BINS).total;
+    if (smem > (size_t)c->max_smem - 1024) return fail(ACOSS_ERR_ARG, "window m=%d too large for the gen-4 sweep", m);
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, T, smem));
+    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep4 cannot be resident (T %d, smem %zu B)", T, smem);
+    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
+    Sweep4Args A;
+    memset(&A, 0, sizeof(A));
+    A.frames = c->frames.as<double>();
+    A.wnorm = c->wnorm.as<double>();
+    A.offs = c->offs.as<int64_t>();
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.counter = d_counter;
+    A.sepk = c->sepk.as<int32_t>();
+    A.sepx = c->sepx.as<double>();
+    A.nb = c->nb.as<uint8_t>();
+    A.m = m;
+    A.gap = c->opt_gap;
+    A.flags = flags;
+    ACOSS_LAUNCH(kfn, grid, T, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
 
 template <int BINS, int MODE>
 int launch_sweep_fast(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter,
@@ -334,7 +385,9 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     // ---- host: work records + item lists
     std::vector<PairWork> W((size_t)n);
     ItemLists L;
-    int64_t sep_total = 0, crp_total = 0, bnd_total = 0;
+    int64_t sep_total = 0, crp_total = 0, bnd_total = 0, nb_total = 0;
+    const bool gen4_ok = c->opt_sweep_gen == 4 && BINS == 12 && !c->opt_force_wide && s4_own_lanes(m) >= 16 &&
+                         (size_t)s4_layout(32 * kFastBuckets, m, BINS).total <= (size_t)c->max_smem - 1024;
     const bool noswap = (flags & kFlagNoSwap) != 0;
     const bool nonmutual = (flags & kFlagNonMutual) != 0;
     for (int p = 0; p < n; ++p) {
@@ -353,7 +406,10 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         w.crp_rows = ok ? (w.swap ? w.N : w.M) : 0;
         w.crp_cols = ok ? (w.swap ? w.M : w.N) : 0;
         w.crp_wp = (w.crp_cols + 31) / 32;
-        w.pad0 = 0;
+        w.expo = 1;
+        w.nb_off = 0;
+        w.nb_stride = 0;
+        w.pad1 = 0;
         w.sep_off = sep_total;
         w.crp_off = crp_total;
         const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
@@ -367,6 +423,19 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             const int dpo = w.swap, other = 1 - dpo;
             const int wB = 256 * kSweepCPL;
             auto Lc_of = [&](int o) { return o ? w.Li : w.Lj; };
+            if (gen4_ok && std::max(w.Li, w.Lj) <= s4_max_cols(m)) {
+                // gen 4: both orientations through the integer-key sweep (a warp contributes own4 columns)
+                const int own4 = s4_own_cols(m);
+                if (!(nonmutual && dpo == 0)) L.g4_0[(Lc_of(other) - 1) / own4].push_back((uint32_t)p * 2 + other);
+                const int b2 = (Lc_of(dpo) - 1) / own4;
+                L.g4_2[b2].push_back((uint32_t)p);
+                L.g4_pack.push_back((uint32_t)p);
+                w.nb_stride = 32 * (b2 + 1);
+                w.nb_off = nb_total;
+                nb_total += ((int64_t)w.crp_rows * w.nb_stride + 15) & ~(int64_t)15;
+                classify_dp(c, L, (uint32_t)p, w.crp_cols);
+                continue;
+            }
             const bool fast_ok = !c->opt_force_wide && std::max((size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows), (size_t)ws_smem_bytes(32 * kFastBuckets, m)) <= (size_t)c->max_smem - 1024;
             if (!(nonmutual && dpo == 0)) {  // column separators of the CRP
                 const int Lc = Lc_of(other);
@@ -403,8 +472,14 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     CU(c->swout.reserve((size_t)n * sizeof(float)));
     CU(c->otiout.reserve((size_t)n * sizeof(int32_t)));
     CU(c->counters.reserve(kCounterSlots * sizeof(unsigned int)));
-    size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size();
-    for (int b = 0; b < kFastBuckets; ++b) n_items += L.fast0[b].size() + L.fast2[b].size();
+    if (!L.g4_pack.empty()) {
+        CU(c->sepk.reserve((size_t)std::max<int64_t>(sep_total, 1) * sizeof(int32_t)));
+        CU(c->sepx.reserve((size_t)std::max<int64_t>(sep_total, 1) * sizeof(double)));
+        CU(c->nb.reserve((size_t)std::max<int64_t>(nb_total, 16)));
+    }
+    size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size();
+    for (int b = 0; b < kFastBuckets; ++b)
+        n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
     CU(c->items.reserve(std::max<size_t>(n_items, 1) * sizeof(uint32_t)));
     // stage: [PairWork...][items...]
     const size_t pw_bytes = (size_t)n * sizeof(PairWork);
@@ -412,6 +487,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     memcpy(c->h_stage.p, W.data(), pw_bytes);
     uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_stage.as<char>() + pw_bytes);
     size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16, pos = 0;
+    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack;
     auto put = [&](const std::vector<uint32_t>& v) {
         size_t at = pos;
         if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
@@ -425,6 +501,9 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     o_dp4 = put(L.dp4);
     o_dp8 = put(L.dp8);
     o_dp16 = put(L.dp16);
+    for (int b = 0; b < kFastBuckets; ++b) o_g40[b] = put(L.g4_0[b]);
+    for (int b = 0; b < kFastBuckets; ++b) o_g42[b] = put(L.g4_2[b]);
+    o_g4pack = put(L.g4_pack);
     CU(cudaMemcpyAsync(c->pairs.p, c->h_stage.p, pw_bytes, cudaMemcpyHostToDevice, c->stream));
     if (n_items)
         CU(cudaMemcpyAsync(c->items.p, hi, n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
@@ -442,15 +521,43 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         c->launches++;
         CU(cudaGetLastError());
     }
-    CU(cudaEventRecord(c->ev[1], c->stream));
     int rc;
+    if (!L.g4_pack.empty()) {
+        // windowed norms for this m (once per upload / window) and the pairs' fixed-point exponents
+        if (c->wnorm_m != m) {
+            CU(c->wnorm.reserve((size_t)std::max<int64_t>(c->total_frames, 1) * sizeof(double)));
+            CU(c->wnmax.reserve((size_t)c->n_songs * sizeof(double)));
+            auto kw = k_wnorm;
+            ACOSS_LAUNCH(kw, c->n_songs, 128, 0, c->stream, c->norms.as<double>(), c->offs.as<int64_t>(),
+                         c->lens.as<int32_t>(), c->n_songs, m, c->wnorm.as<double>(), c->wnmax.as<double>());
+            c->launches++;
+            CU(cudaGetLastError());
+            c->wnorm_m = m;
+        }
+        auto ke = k_expo;
+        ACOSS_LAUNCH(ke, (n + 127) / 128, 128, 0, c->stream, c->pairs.as<PairWork>(), n, c->wnmax.as<double>());
+        c->launches++;
+        CU(cudaGetLastError());
+    }
+    CU(cudaEventRecord(c->ev[1], c->stream));
     // largest buckets first: their CTAs are the long ones
     for (int b = kFastBuckets - 1; b >= 0; --b)
-        if ((rc = (c->opt_sweep_gen == 2 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
+    for (int b = kFastBuckets - 1; b >= 0; --b)
+        if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
     if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
     for (int b = kFastBuckets - 1; b >= 0; --b)
-        if ((rc = (c->opt_sweep_gen == 2 ? launch_sweep_fast<BINS, 2> : launch_sweep_ws<BINS, 2>)(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep4<12, 2>(c, d_items + o_g42[b], (int)L.g4_2[b].size(), b, m, d_cnt + 32 + kFastBuckets + b, flags))) return rc;
+    if (!L.g4_pack.empty()) {
+        auto kp = k_nb_to_packed;
+        ACOSS_LAUNCH(kp, (int)L.g4_pack.size(), 128, 0, c->stream, c->pairs.as<PairWork>(), d_items + o_g4pack,
+                     (int)L.g4_pack.size(), c->nb.as<uint8_t>(), c->crp.as<uint32_t>(), m);
+        c->launches++;
+        CU(cudaGetLastError());
+    }
+    for (int b = kFastBuckets - 1; b >= 0; --b)
+        if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 2> : launch_sweep_ws<BINS, 2>)(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
     if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
     CU(cudaEventRecord(c->ev[3], c->stream));
     if ((rc = run_dp_lists(c, L, d_items, o_dp4, o_dp8, o_dp16, flags))) return rc;
@@ -538,7 +645,8 @@ int acoss_destroy(acoss_ctx* c) {
     cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->frames, &c->norms, &c->offs, &c->gchroma, &c->pairs, &c->items, &c->counters,
                       &c->seps, &c->crp, &c->bnd, &c->qout, &c->dout, &c->swout, &c->otiout, &c->gscratch,
-                      &c->dense_in, &c->dense_desc, &c->dense_starts};
+                      &c->dense_in, &c->dense_desc, &c->dense_starts,
+                      &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb};
     for (DevBuf* b : bufs) b->release();
     c->h_stage.release();
     for (int i = 0; i < 5; ++i)
@@ -583,6 +691,9 @@ int acoss_upload_songs(acoss_ctx* c, const void* frames, int dtype, const int64_
         }
     }
     CU(cudaMemcpyAsync(c->offs.p, offsets, (size_t)n_songs * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+    CU(c->lens.reserve((size_t)n_songs * sizeof(int32_t)));
+    CU(cudaMemcpyAsync(c->lens.p, lengths, (size_t)n_songs * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    c->wnorm_m = -1;
     if (total) {
         auto kfn = k_norms<double>;
         ACOSS_LAUNCH(kfn, (total + 255) / 256, 256, 0, c->stream, c->frames.as<double>(), c->norms.as<double>(), total,
@@ -621,14 +732,16 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
     while (p0 < P) {
         // cut a chunk whose scratch fits the budget
         int n = 0;
-        int64_t sep = 0, crp = 0;
+        int64_t sep = 0, crp = 0, nbb = 0;
         while (p0 + n < P && n < c->opt_chunk_pairs) {
             const int Li = c->h_len[pairs[2 * (p0 + n)]], Lj = c->h_len[pairs[2 * (p0 + n) + 1]];
             const int64_t M = std::max(Li - m + 1, 0), N = std::max(Lj - m + 1, 0);
             const int64_t s2 = M + N, c2 = std::max(M, N) * ((std::min(M, N) + 31) / 32 + 1);
-            if (n > 0 && (sep + s2 > kMaxChunkSepDoubles || crp + c2 > kMaxChunkCrpWords)) break;
+            const int64_t n2 = std::max(M, N) * (((std::min(Li, Lj) + 99) / 100) * 32) + 16;
+            if (n > 0 && (sep + s2 > kMaxChunkSepDoubles || crp + c2 > kMaxChunkCrpWords || nbb + n2 > kMaxChunkNbBytes)) break;
             sep += s2;
             crp += c2;
+            nbb += n2;
             ++n;
         }
         if (c->bins == 12)
@@ -871,8 +984,11 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
     else if (n == "force_gscratch")
         c->opt_force_gscratch = value != 0;
     else if (n == "sweep_gen") {
-        if (value != 2 && value != 3) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2 or 3");
+        if (value != 2 && value != 3 && value != 4) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2, 3 or 4");
         c->opt_sweep_gen = (int)value;
+    } else if (n == "gap_units") {
+        if (value < 2 || value > (1 << 24)) return fail(ACOSS_ERR_ARG, "gap_units must be in [2, 2^24]");
+        c->opt_gap = (int)value;
     } else if (n == "debug_flags")
         c->opt_debug_flags = (uint32_t)value;
     else if (n == "dp_max_cpl") {

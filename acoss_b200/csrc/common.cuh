@@ -42,10 +42,14 @@ struct PairWork {
     int32_t k_row, k_col;    // neighbours kept per row (out of N) / per column (out of M)
     int32_t oti;             // filled by k_oti
     int32_t swap;            // 1: CRP + DP run on the transpose (rows = song_j windows)
-    int32_t crp_rows, crp_cols, crp_wp, pad0;  // stored CRP shape, words per row
-    int64_t sep_off;         // into seps (doubles)
+    int32_t crp_rows, crp_cols, crp_wp;  // stored CRP shape, words per row
+    int32_t expo;            // fixed-point exponent e of the pair's integer keys (k_expo, kernels_sweep4.cuh)
+    int64_t sep_off;         // into seps (doubles) / sepk (int32) / sepx (doubles)
     int64_t crp_off;         // into crp (uint32 words)
     int64_t bnd_off;         // into the DP boundary scratch (int4 records), -1 when unused
+    int64_t nb_off;          // into the nibble-byte CRP arena of the gen-4 sweep (bytes)
+    int32_t nb_stride;       // bytes per row there (= threads of the MODE 2 CTA)
+    int32_t pad1;
 };
 
 // Named barriers (PTX bar.sync / bar.arrive with an explicit thread count): the producer /

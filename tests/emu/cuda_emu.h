@@ -344,6 +344,26 @@ inline int __reduce_max_sync(unsigned, int v) {
     emu::warp_barrier();
     return r;
 }
+inline unsigned __reduce_min_sync(unsigned, unsigned v) {
+    emu::Warp& w = emu::my_warp();
+    w.slot[emu::lane_id()] = (uint64_t)v;
+    emu::warp_barrier();
+    unsigned r = (unsigned)w.slot[0];
+    for (int l = 1; l < 32; ++l) r = std::min(r, (unsigned)w.slot[l]);
+    emu::warp_barrier();
+    return r;
+}
+inline unsigned __reduce_max_sync(unsigned, unsigned v) {
+    emu::Warp& w = emu::my_warp();
+    w.slot[emu::lane_id()] = (uint64_t)v;
+    emu::warp_barrier();
+    unsigned r = (unsigned)w.slot[0];
+    for (int l = 1; l < 32; ++l) r = std::max(r, (unsigned)w.slot[l]);
+    emu::warp_barrier();
+    return r;
+}
+inline int __double2loint(double v) { return (int)(uint32_t)(emu::to_bits(v) & 0xffffffffu); }
+inline int __double2hiint(double v) { return (int)(uint32_t)(emu::to_bits(v) >> 32); }
 inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }
 inline int __all_sync(unsigned m, int pred) { return __ballot_sync(m, pred) == 0xffffffffu; }
 
