@@ -21,6 +21,7 @@
 #include "kernels_sweep2.cuh"
 #include "kernels_sweep3.cuh"
 #include "kernels_sweep4.cuh"
+#include "kernels_sweep5.cuh"
 
 #ifdef ACOSS_EMU
 #define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
@@ -134,7 +135,9 @@ struct acoss_ctx {
     int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
                                  // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
     int opt_chunk_pairs = 1 << 18;
-    int opt_sweep_gen = 4;         // 4: integer-key sweep (kernels_sweep4.cuh, default); 2: float64-selection sweep
+    int opt_sweep_gen = 5;         // 5: warp-specialised integer-key sweep (kernels_sweep5.cuh, default; falls back
+                                   // to 4 for windows other than 9 and column songs over 960 frames);
+                                   // 4: integer-key sweep (kernels_sweep4.cuh); 2: float64-selection sweep
                                    // (kernels_sweep2.cuh); 3: warp-specialised variant of 2 (kernels_sweep3.cuh)
     int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
     uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
@@ -157,6 +160,7 @@ struct ItemLists {
     std::vector<uint32_t> fast0[kFastBuckets], fast2[kFastBuckets];  // fast sweep: separators / separators + CRP
     std::vector<uint32_t> wide0, wide1;                              // general sweep (long songs): MODE 0 / MODE 1
     std::vector<uint32_t> g4_0[kFastBuckets], g4_2[kFastBuckets];    // gen-4 sweep: separators / CRP
+    std::vector<uint32_t> g5_0[2], g5_2[2];                          // gen-5 sweep, 4 / 8 compute warps
     std::vector<uint32_t> g4_pack;                                   // pairs whose nibble CRP needs packing
     std::vector<uint32_t> dp4, dp8, dp16;
     int wide0_w = 0, wide1_w = 0;
@@ -324,6 +328,38 @@ int launch_sweep(acoss_ctx* c, const uint32_t* d_items, int n_items, int Wmax, i
     return ACOSS_OK;
 }
 
+template <int MODE>
+int launch_sweep5(acoss_ctx* c, const uint32_t* d_items, int n_items, int nwg, int m, unsigned int* d_counter, uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    auto kfn = (nwg == 1) ? k_sweep5<12, MODE, 9, 1> : k_sweep5<12, MODE, 9, 2>;
+    const int threads = 256 * nwg;
+    const size_t smem = (size_t)s5_layout(4 * nwg, m, 12).total;
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, threads, smem));
+    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep5 cannot be resident (threads %d, smem %zu B)", threads, smem);
+    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
+    Sweep4Args A;
+    memset(&A, 0, sizeof(A));
+    A.frames = c->frames.as<double>();
+    A.wnorm = c->wnorm.as<double>();
+    A.offs = c->offs.as<int64_t>();
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.counter = d_counter;
+    A.sepk = c->sepk.as<int32_t>();
+    A.sepx = c->sepx.as<double>();
+    A.nb = c->nb.as<uint8_t>();
+    A.m = m;
+    A.gap = c->opt_gap;
+    A.flags = flags;
+    ACOSS_LAUNCH(kfn, grid, threads, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
 template <int CPL>
 int launch_dp(acoss_ctx* c, const uint32_t* d_items, int n_items, uint32_t flags, float* q, float* d, float* sw) {
     if (n_items <= 0) return ACOSS_OK;
@@ -386,7 +422,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     std::vector<PairWork> W((size_t)n);
     ItemLists L;
     int64_t sep_total = 0, crp_total = 0, bnd_total = 0, nb_total = 0;
-    const bool gen4_ok = c->opt_sweep_gen == 4 && BINS == 12 && !c->opt_force_wide && s4_own_lanes(m) >= 16 &&
+    const bool gen4_ok = c->opt_sweep_gen >= 4 && BINS == 12 && !c->opt_force_wide && s4_own_lanes(m) >= 16 &&
                          (size_t)s4_layout(32 * kFastBuckets, m, BINS).total <= (size_t)c->max_smem - 1024;
     const bool noswap = (flags & kFlagNoSwap) != 0;
     const bool nonmutual = (flags & kFlagNonMutual) != 0;
@@ -426,11 +462,22 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             if (gen4_ok && std::max(w.Li, w.Lj) <= s4_max_cols(m)) {
                 // gen 4: both orientations through the integer-key sweep (a warp contributes own4 columns)
                 const int own4 = s4_own_cols(m);
-                if (!(nonmutual && dpo == 0)) L.g4_0[(Lc_of(other) - 1) / own4].push_back((uint32_t)p * 2 + other);
-                const int b2 = (Lc_of(dpo) - 1) / own4;
-                L.g4_2[b2].push_back((uint32_t)p);
+                const bool g5 = c->opt_sweep_gen == 5 && m == 9;  // the warp-specialised kernels are built for m = 9
+                const int b0 = (Lc_of(other) - 1) / own4, b2 = (Lc_of(dpo) - 1) / own4;  // compute warps needed - 1
+                if (!(nonmutual && dpo == 0)) {
+                    if (g5 && b0 < 8)
+                        L.g5_0[b0 / 4].push_back((uint32_t)p * 2 + other);
+                    else
+                        L.g4_0[b0].push_back((uint32_t)p * 2 + other);
+                }
+                if (g5 && b2 < 8) {
+                    L.g5_2[b2 / 4].push_back((uint32_t)p);
+                    w.nb_stride = 128 * (b2 / 4 + 1);
+                } else {
+                    L.g4_2[b2].push_back((uint32_t)p);
+                    w.nb_stride = 32 * (b2 + 1);
+                }
                 L.g4_pack.push_back((uint32_t)p);
-                w.nb_stride = 32 * (b2 + 1);
                 w.nb_off = nb_total;
                 nb_total += ((int64_t)w.crp_rows * w.nb_stride + 15) & ~(int64_t)15;
                 classify_dp(c, L, (uint32_t)p, w.crp_cols);
@@ -480,6 +527,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size();
     for (int b = 0; b < kFastBuckets; ++b)
         n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
+    for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
     CU(c->items.reserve(std::max<size_t>(n_items, 1) * sizeof(uint32_t)));
     // stage: [PairWork...][items...]
     const size_t pw_bytes = (size_t)n * sizeof(PairWork);
@@ -487,7 +535,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     memcpy(c->h_stage.p, W.data(), pw_bytes);
     uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_stage.as<char>() + pw_bytes);
     size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16, pos = 0;
-    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack;
+    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2];
     auto put = [&](const std::vector<uint32_t>& v) {
         size_t at = pos;
         if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
@@ -504,6 +552,8 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     for (int b = 0; b < kFastBuckets; ++b) o_g40[b] = put(L.g4_0[b]);
     for (int b = 0; b < kFastBuckets; ++b) o_g42[b] = put(L.g4_2[b]);
     o_g4pack = put(L.g4_pack);
+    for (int b = 0; b < 2; ++b) o_g50[b] = put(L.g5_0[b]);
+    for (int b = 0; b < 2; ++b) o_g52[b] = put(L.g5_2[b]);
     CU(cudaMemcpyAsync(c->pairs.p, c->h_stage.p, pw_bytes, cudaMemcpyHostToDevice, c->stream));
     if (n_items)
         CU(cudaMemcpyAsync(c->items.p, hi, n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
@@ -541,12 +591,16 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     }
     CU(cudaEventRecord(c->ev[1], c->stream));
     // largest buckets first: their CTAs are the long ones
+    for (int b = 1; b >= 0; --b)
+        if (BINS == 12 && (rc = launch_sweep5<0>(c, d_items + o_g50[b], (int)L.g5_0[b].size(), b + 1, m, d_cnt + 56 + b, flags))) return rc;
     for (int b = kFastBuckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
     for (int b = kFastBuckets - 1; b >= 0; --b)
         if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
     if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
+    for (int b = 1; b >= 0; --b)
+        if (BINS == 12 && (rc = launch_sweep5<2>(c, d_items + o_g52[b], (int)L.g5_2[b].size(), b + 1, m, d_cnt + 58 + b, flags))) return rc;
     for (int b = kFastBuckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep4<12, 2>(c, d_items + o_g42[b], (int)L.g4_2[b].size(), b, m, d_cnt + 32 + kFastBuckets + b, flags))) return rc;
     if (!L.g4_pack.empty()) {
@@ -737,7 +791,7 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
             const int Li = c->h_len[pairs[2 * (p0 + n)]], Lj = c->h_len[pairs[2 * (p0 + n) + 1]];
             const int64_t M = std::max(Li - m + 1, 0), N = std::max(Lj - m + 1, 0);
             const int64_t s2 = M + N, c2 = std::max(M, N) * ((std::min(M, N) + 31) / 32 + 1);
-            const int64_t n2 = std::max(M, N) * (((std::min(Li, Lj) + 99) / 100) * 32) + 16;
+            const int64_t n2 = std::max(M, N) * (((std::min(Li, Lj) + 99) / 100) * 32 + 128) + 16;
             if (n > 0 && (sep + s2 > kMaxChunkSepDoubles || crp + c2 > kMaxChunkCrpWords || nbb + n2 > kMaxChunkNbBytes)) break;
             sep += s2;
             crp += c2;
@@ -984,7 +1038,7 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
     else if (n == "force_gscratch")
         c->opt_force_gscratch = value != 0;
     else if (n == "sweep_gen") {
-        if (value != 2 && value != 3 && value != 4) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2, 3 or 4");
+        if (value < 2 || value > 5) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2, 3, 4 or 5");
         c->opt_sweep_gen = (int)value;
     } else if (n == "gap_units") {
         if (value < 2 || value > (1 << 24)) return fail(ACOSS_ERR_ARG, "gap_units must be in [2, 2^24]");

@@ -482,6 +482,218 @@ __device__ __noinline__ bool s4_resolve_unsafe(const uint4* __restrict__ row4, i
     return zin < zout;
 }
 
+// ---------------------------------------------------------------- one strip row, one warp
+// Selects the row's separator and, MODE 0: exports it (absolute key units, flagged rows with
+// their float64 value); MODE 2: turns the row into CRP nibbles using the column separators.
+struct S4RowArgs {
+    const uint4* row4;   // the strip row (nq * 32 quads)
+    int nq, srow, nrows; // quads per lane, row within the strip, rows in the strip
+    int irow, lane;      // window index within the row song
+    int kk, No, m, G, BANDW;
+    bool use_row;
+    const double* rwn;   // windowed norms of the row song
+    double BIGE;
+    int64_t rsep_off;
+    int64_t csep_off;    // column separators of the item (MODE 2)
+    int* misc;           // misc[2..5] separator history, misc[8..9] its counts, misc[10] flag-list overflow
+    int spar;
+    int* cand_s;         // per-warp scratch: 2 * kS4MaxFlag ints
+    int* s_wcnt;
+    const int* fcol;     // flagged columns of the item
+    const int* fblo;
+    const double* fsepx;
+    const int* csk_s;    // column separators (certainly-in bounds)
+    int nflag;
+    int64_t nb_off;
+    int nb_stride;
+};
+
+template <int BINS, int MODE, int NQ>
+__device__ __forceinline__ void s4_resolve_row(const Sweep4Args& A, const S4Pair& pp, const S4RowArgs& R, S4Sel& st) {
+    const int irow = R.irow, lane = R.lane, warp = R.srow, nrows = R.nrows, m = R.m, kk = R.kk, No = R.No;
+    const int G = R.G, BANDW = R.BANDW, nflag = R.nflag, orient = pp.orient, spar = R.spar, NW = R.nq;
+    int* const misc = R.misc;
+    int* const hist = misc + 2;
+    int* const cand_s = R.cand_s;
+    const int* const fcol = R.fcol;
+    const int* const fblo = R.fblo;
+    const double* const fsepx = R.fsepx;
+    const int* const csk_s = R.csk_s;
+    const bool use_row = R.use_row;
+    const int64_t rsep_off = R.rsep_off;
+    const uint4* row4 = R.row4;
+    const int kwx = s4_fix(R.rwn[irow + m - 1] + R.BIGE);
+    int thr = kKeyInf - 1;  // row-relative certainly-in bound
+    bool rflag = false;
+    double rsepx = 0.0;
+    int rblo = 0, ncand = 0;
+    unsigned cand_in = 0;
+    if (kk <= 0) {
+        thr = -1;
+    } else if (A.flags & (1u << 30)) {
+        thr = 1 << 30;  // profiling knob: no selection (results are meaningless)
+    } else if (kk < No && (MODE == 0 || use_row)) {
+        int vk, vk1;
+        S4Keys<NQ> keys;
+        keys.load(row4, lane, NW);
+        // guess: the previous strip's last separator, extrapolated by half its last step
+        const int nh = misc[8 + (spar ^ 1)];
+        int g = 0;
+        if (nh >= 1) {
+            const int tl = hist[2 * (spar ^ 1)];
+            g = tl;
+            if (nh >= 2) g += ((tl - hist[2 * (spar ^ 1) + 1]) * (warp + 1)) / 2;
+        }
+        s4_select(keys, kk, No, g - kwx, nh >= 1, st, lane, vk, vk1);
+        if (lane == 0) {
+            if (warp == nrows - 1) hist[2 * spar] = vk + kwx;
+            if (warp == nrows - 2) hist[2 * spar + 1] = vk + kwx;
+            if (warp == 0) misc[8 + spar] = nrows >= 2 ? 2 : 1;
+        }
+        const int gap = vk1 - vk;
+        if (gap >= 2 * G) {
+            thr = vk + (gap >> 1);
+        } else {
+            const bool ok = s4_resolve_unsafe(row4, NW, kk, vk, vk1, pp, irow, m, lane, cand_s, R.s_wcnt, rsepx,
+                                              ncand, cand_in);
+            if (ok) {
+                rflag = true;
+                rblo = vk - 3;
+                thr = rblo - 1;
+            } else {
+                thr = vk;  // tie cluster: the reference's own choice is undefined here
+                ncand = 0;
+            }
+        }
+    }
+    if (MODE == 0) {
+        if (lane == 0) {
+            if (rflag) {
+                A.sepk[rsep_off + irow] = -(rblo + kwx) - 1;
+                A.sepx[rsep_off + irow] = rsepx;
+            } else {
+                // kk <= 0 -> -1 ... never in; kk >= No -> everything valid
+                A.sepk[rsep_off + irow] = (thr < 0) ? 0 : ((thr >= kKeyInf - 1) ? kKeyInf - 1 : thr + kwx);
+                if (thr < 0) A.sepk[rsep_off + irow] = 0;
+            }
+        }
+    } else {
+        // ---- patch list: cells of flagged bands decided in float64
+        int npatch = 0;
+        int* patch_cols = cand_s + kS4MaxFlag;
+        if (rflag || nflag > 0) {
+            // candidates: the unsafe row's band cells (slots 0..ncand-1 of cand_s), then
+            // this row's cell of every flagged column
+            const int ntot = ncand + nflag;
+            for (int base = 0; base < ntot; base += 32) {
+                const int c = base + lane;
+                bool setbit = false;
+                int col = 0;
+                if (c < ntot) {
+                    const bool from_row = c < ncand;
+                    col = from_row ? cand_s[c] : fcol[c - ncand];
+                    const int key = ((const int*)row4)[col];
+                    const int kabs = key + kwx;
+                    // column test
+                    int f = -1;
+                    for (int q = 0; q < nflag; ++q)
+                        if (fcol[q] == col) f = q;
+                    double zx = 0.0;
+                    bool have_z = false;
+                    bool colin, rowin;
+                    if (f >= 0) {
+                        if (kabs < fblo[f]) colin = true;
+                        else if (kabs > fblo[f] + BANDW) colin = false;
+                        else {
+                            const int jwin = col - (m - 1);
+                            zx = orient ? s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, jwin, irow)
+                                        : s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, irow, jwin);
+                            have_z = true;
+                            colin = zx <= fsepx[f];
+                        }
+                    } else {
+                        colin = kabs <= csk_s[col];
+                    }
+                    if (rflag) {
+                        if (key < rblo) rowin = true;
+                        else if (key > rblo + BANDW) rowin = false;
+                        else {
+                            if (!have_z) {
+                                const int jwin = col - (m - 1);
+                                zx = orient ? s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, jwin, irow)
+                                            : s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, irow, jwin);
+                            }
+                            rowin = zx <= rsepx;
+                        }
+                    } else {
+                        rowin = key <= thr;
+                    }
+                    setbit = colin && rowin && key != kKeyInf;
+                }
+                const unsigned sb = __ballot_sync(kFullMask, setbit);
+                if (setbit) {
+                    const int pos = npatch + __popc(sb & ((1u << lane) - 1u));
+                    if (pos < kS4MaxFlag) patch_cols[pos] = col;
+                }
+                npatch += __popc(sb);
+            }
+            if (npatch > kS4MaxFlag) npatch = kS4MaxFlag;
+            __syncwarp();
+        }
+        // ---- bits: nibble per (lane, quad), one byte per thread-quad of the row
+        uint8_t* out = A.nb + R.nb_off + (int64_t)irow * R.nb_stride;
+        const uint4* csk4 = reinterpret_cast<const uint4*>(csk_s);
+        for (int q = 0; q < NW; ++q) {
+            const int tq = lane + 32 * q;
+            const uint4 kv = row4[tq];
+            const uint4 cv = csk4[tq];
+            unsigned nib = 0;
+            nib |= ((int)kv.x <= imin(thr, (int)cv.x - kwx)) ? 1u : 0u;
+            nib |= ((int)kv.y <= imin(thr, (int)cv.y - kwx)) ? 2u : 0u;
+            nib |= ((int)kv.z <= imin(thr, (int)cv.z - kwx)) ? 4u : 0u;
+            nib |= ((int)kv.w <= imin(thr, (int)cv.w - kwx)) ? 8u : 0u;
+            if (misc[10] != 0 && (int)(cv.x | cv.y | cv.z | cv.w) < 0) {
+                // generic path (only when the item has more flagged columns than the patch list
+                // holds): a negative entry is a flagged column that is not in the list
+                const int kvv[4] = {(int)kv.x, (int)kv.y, (int)kv.z, (int)kv.w};
+                const int cvv[4] = {(int)cv.x, (int)cv.y, (int)cv.z, (int)cv.w};
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    if (cvv[c] >= -1 || kvv[c] == kKeyInf) continue;  // -1 marks a column outside the plot
+                    const int blo = -cvv[c] - 1, kabs = kvv[c] + kwx, col = 4 * tq + c;
+                    const int jwin = col - (m - 1);
+                    bool colin;
+                    if (kabs < blo) colin = true;
+                    else if (kabs > blo + BANDW) colin = false;
+                    else {
+                        const double zx = orient ? s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, jwin, irow)
+                                                 : s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, irow, jwin);
+                        colin = zx <= A.sepx[R.csep_off + jwin];
+                    }
+                    bool rowin;
+                    if (rflag && kvv[c] >= rblo) {
+                        if (kvv[c] > rblo + BANDW) rowin = false;
+                        else {
+                            const double zx = orient ? s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, jwin, irow)
+                                                     : s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, irow, jwin);
+                            rowin = zx <= rsepx;
+                        }
+                    } else {
+                        rowin = kvv[c] <= thr;
+                    }
+                    if (colin && rowin) nib |= 1u << c;
+                }
+            }
+            for (int p = 0; p < npatch; ++p) {
+                const int col = patch_cols[p];
+                if ((col >> 2) == tq) nib |= 1u << (col & 3);
+            }
+            out[tq] = (uint8_t)nib;
+        }
+    }
+
+}
+
 // ---------------------------------------------------------------- the kernel
 // MW > 0: compile-time embedding window; MW == 0: read from the arguments.
 // NQ > 0: the CTA has exactly 32 NQ threads and a selecting warp keeps its row's keys in
@@ -541,6 +753,7 @@ __global__ void ACOSS_MAXNREG4(168) k_sweep4(Sweep4Args A) {
         if (tid == 0) {
             *s_item = (int)atomicAdd(A.counter, 1u);
             *s_nflag = 0;
+            misc[10] = 0;
         }
         __syncthreads();
         const int it = *s_item;
@@ -634,9 +847,9 @@ __global__ void ACOSS_MAXNREG4(168) k_sweep4(Sweep4Args A) {
                             fsepx[slot] = A.sepx[csep_off + j];
                             v = blo - 1;  // certainly-in bound; the band is patched per row
                         } else {
-                            // more flagged columns than the patch list holds (tie clusters): keep
-                            // the key-level separator of the band's lower part
-                            v = blo + 3;
+                            // more flagged columns than the patch list holds: the encoded (negative) value stays
+                            // and the row code takes its generic per-cell path for them
+                            misc[10] = 1;
                         }
                     }
                 }
@@ -754,145 +967,35 @@ __global__ void ACOSS_MAXNREG4(168) k_sweep4(Sweep4Args A) {
             si = 0;
             __syncthreads();  // every warp has delivered its part of the strip
             if (warp < nrows) {
-                const int irow = i - (nrows - 1) + warp;  // window index within the row song
-                const uint4* row4 = strip4 + warp * T;
-                const int kwx = s4_fix(rwn[irow + m - 1] + BIGE);
-                int thr = kKeyInf - 1;  // row-relative certainly-in bound
-                bool rflag = false;
-                double rsepx = 0.0;
-                int rblo = 0, ncand = 0;
-                unsigned cand_in = 0;
-                if (kk <= 0) {
-                    thr = -1;
-                } else if (A.flags & (1u << 30)) {
-                    thr = 1 << 30;  // profiling knob: no selection (results are meaningless)
-                } else if (kk < No && (MODE == 0 || use_row)) {
-                    int vk, vk1;
-                    S4Keys<NQ> keys;
-                    keys.load(row4, lane, NW);
-                    // guess: the previous strip's last separator, extrapolated by half its last step
-                    const int nh = misc[8 + (spar ^ 1)];
-                    int g = 0;
-                    if (nh >= 1) {
-                        const int tl = hist[2 * (spar ^ 1)];
-                        g = tl;
-                        if (nh >= 2) g += ((tl - hist[2 * (spar ^ 1) + 1]) * (warp + 1)) / 2;
-                    }
-                    s4_select(keys, kk, No, g - kwx, nh >= 1, st, lane, vk, vk1);
-                    if (lane == 0) {
-                        if (warp == nrows - 1) hist[2 * spar] = vk + kwx;
-                        if (warp == nrows - 2) hist[2 * spar + 1] = vk + kwx;
-                        if (warp == 0) misc[8 + spar] = nrows >= 2 ? 2 : 1;
-                    }
-                    const int gap = vk1 - vk;
-                    if (gap >= 2 * G) {
-                        thr = vk + (gap >> 1);
-                    } else {
-                        const bool ok = s4_resolve_unsafe(row4, NW, kk, vk, vk1, pp, irow, m, lane, cand_s, s_wcnt, rsepx,
-                                                          ncand, cand_in);
-                        if (ok) {
-                            rflag = true;
-                            rblo = vk - 3;
-                            thr = rblo - 1;
-                        } else {
-                            thr = vk;  // tie cluster: the reference's own choice is undefined here
-                            ncand = 0;
-                        }
-                    }
-                }
-                if (MODE == 0) {
-                    if (lane == 0) {
-                        if (rflag) {
-                            A.sepk[rsep_off + irow] = -(rblo + kwx) - 1;
-                            A.sepx[rsep_off + irow] = rsepx;
-                        } else {
-                            // kk <= 0 -> -1 ... never in; kk >= No -> everything valid
-                            A.sepk[rsep_off + irow] = (thr < 0) ? 0 : ((thr >= kKeyInf - 1) ? kKeyInf - 1 : thr + kwx);
-                            if (thr < 0) A.sepk[rsep_off + irow] = 0;
-                        }
-                    }
-                } else {
-                    // ---- patch list: cells of flagged bands decided in float64
-                    int npatch = 0;
-                    int* patch_cols = cand_s + kS4MaxFlag;
-                    if (rflag || nflag > 0) {
-                        // candidates: the unsafe row's band cells (slots 0..ncand-1 of cand_s), then
-                        // this row's cell of every flagged column
-                        const int ntot = ncand + nflag;
-                        for (int base = 0; base < ntot; base += 32) {
-                            const int c = base + lane;
-                            bool setbit = false;
-                            int col = 0;
-                            if (c < ntot) {
-                                const bool from_row = c < ncand;
-                                col = from_row ? cand_s[c] : fcol[c - ncand];
-                                const int key = ((const int*)row4)[col];
-                                const int kabs = key + kwx;
-                                // column test
-                                int f = -1;
-                                for (int q = 0; q < nflag; ++q)
-                                    if (fcol[q] == col) f = q;
-                                double zx = 0.0;
-                                bool have_z = false;
-                                bool colin, rowin;
-                                if (f >= 0) {
-                                    if (kabs < fblo[f]) colin = true;
-                                    else if (kabs > fblo[f] + BANDW) colin = false;
-                                    else {
-                                        const int jwin = col - (m - 1);
-                                        zx = orient ? s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, jwin, irow)
-                                                    : s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, irow, jwin);
-                                        have_z = true;
-                                        colin = zx <= fsepx[f];
-                                    }
-                                } else {
-                                    colin = kabs <= csk_s[col];
-                                }
-                                if (rflag) {
-                                    if (key < rblo) rowin = true;
-                                    else if (key > rblo + BANDW) rowin = false;
-                                    else {
-                                        if (!have_z) {
-                                            const int jwin = col - (m - 1);
-                                            zx = orient ? s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, jwin, irow)
-                                                        : s4_cell_exact(pp.fi, pp.fj, BINS, pp.oti, m, irow, jwin);
-                                        }
-                                        rowin = zx <= rsepx;
-                                    }
-                                } else {
-                                    rowin = key <= thr;
-                                }
-                                setbit = colin && rowin && key != kKeyInf;
-                            }
-                            const unsigned sb = __ballot_sync(kFullMask, setbit);
-                            if (setbit) {
-                                const int pos = npatch + __popc(sb & ((1u << lane) - 1u));
-                                if (pos < kS4MaxFlag) patch_cols[pos] = col;
-                            }
-                            npatch += __popc(sb);
-                        }
-                        if (npatch > kS4MaxFlag) npatch = kS4MaxFlag;
-                        __syncwarp();
-                    }
-                    // ---- bits: nibble per (lane, quad), one byte per thread-quad of the row
-                    uint8_t* out = A.nb + pw.nb_off + (int64_t)irow * pw.nb_stride;
-                    const uint4* csk4 = reinterpret_cast<const uint4*>(csk_s);
-                    for (int q = 0; q < NW; ++q) {
-                        const int tq = lane + 32 * q;
-                        const uint4 kv = row4[tq];
-                        const uint4 cv = csk4[tq];
-                        unsigned nib = 0;
-                        nib |= ((int)kv.x <= imin(thr, (int)cv.x - kwx)) ? 1u : 0u;
-                        nib |= ((int)kv.y <= imin(thr, (int)cv.y - kwx)) ? 2u : 0u;
-                        nib |= ((int)kv.z <= imin(thr, (int)cv.z - kwx)) ? 4u : 0u;
-                        nib |= ((int)kv.w <= imin(thr, (int)cv.w - kwx)) ? 8u : 0u;
-                        for (int p = 0; p < npatch; ++p) {
-                            const int col = patch_cols[p];
-                            if ((col >> 2) == tq) nib |= 1u << (col & 3);
-                        }
-                        out[tq] = (uint8_t)nib;
-                    }
-                }
+                S4RowArgs ra;
+                ra.row4 = strip4 + warp * T;
+                ra.nq = NW;
+                ra.srow = warp;
+                ra.nrows = nrows;
+                ra.irow = i - (nrows - 1) + warp;  // window index within the row song
+                ra.lane = lane;
+                ra.kk = kk;
+                ra.No = No;
+                ra.m = m;
+                ra.G = G;
+                ra.BANDW = BANDW;
+                ra.use_row = use_row;
+                ra.rwn = rwn;
+                ra.BIGE = BIGE;
+                ra.rsep_off = rsep_off;
+                ra.csep_off = csep_off;
+                ra.misc = misc;
+                ra.spar = spar;
+                ra.cand_s = cand_s;
+                ra.s_wcnt = s_wcnt;
+                ra.fcol = fcol;
+                ra.fblo = fblo;
+                ra.fsepx = fsepx;
+                ra.csk_s = csk_s;
+                ra.nflag = nflag;
+                ra.nb_off = pw.nb_off;
+                ra.nb_stride = pw.nb_stride;
+                s4_resolve_row<BINS, MODE, NQ>(A, pp, ra, st);
             }
             spar ^= 1;
             __syncthreads();

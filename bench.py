@@ -47,7 +47,10 @@ def parse_args():
     ap.add_argument("--impl", choices=("b200", "reference"), default="b200")
     ap.add_argument("--songs", type=int, default=10000, help="songs of the whatisacover-shaped set")
     ap.add_argument("--pairs-per-step", type=int, default=200000, help="pairs per rank per step")
-    ap.add_argument("--cpu-pairs", type=int, default=0, help="pairs of the CPU sample (0: 6 per core)")
+    ap.add_argument("--cpu-pairs", type=int, default=0,
+                    help="pairs of the CPU sample (0: 800 per core in the default arm = 15-25 s of CPU work, "
+                         "150 per core and step in the reference arm)")
+    ap.add_argument("--sweep-gen", type=int, default=0, help="force a sweep generation (2, 4, 5); 0 = library default")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -173,7 +176,7 @@ def run_reference(args, rank, world):
     songs, _ = make_workload(args.songs)
     lengths = np.array([s["chroma"].shape[1] for s in songs])
     cores = os.cpu_count() or 1
-    n = args.cpu_pairs or max(16, 4 * cores)
+    n = args.cpu_pairs or max(64, 150 * cores)
     times, npairs, qcells = [], 0, 0
     for s in range(args.warmup + args.steps):
         pairs = step_pairs(args.songs, n, 10_000 + s, 0, 1)
@@ -228,7 +231,7 @@ def run_b200(args, rank, world, local):
         if world == 1 and not args.no_cpu_baseline:
             # CPU arm first: its worker processes are forked before this process touches CUDA
             cores = os.cpu_count() or 1
-            n = args.cpu_pairs or max(16, 6 * cores)
+            n = args.cpu_pairs or max(64, 800 * cores)
             secs = cpu_reference_run(songs, step_pairs(args.songs, n, 10_000, 0, 1), cores)
             cpu_base = {"value": n / secs, "unit": "pairs/s", "cores": cores, "kind": "port",
                         "sample": cpu_sample_desc(n, cores), "seconds": secs}
@@ -248,6 +251,8 @@ def run_b200(args, rank, world, local):
     alg = Serra09(songs=songs, labels=labels, shortname="bench", do_memmaps=False, do_mfcc=False, device=local)
     alg.preload()
     ctx, slot = alg._context_for("chroma", np.arange(args.songs))
+    if args.sweep_gen:
+        ctx.set_option("sweep_gen", args.sweep_gen)
     B = args.pairs_per_step
 
     # ---- value: C-ABI call, songs resident in HBM
@@ -326,9 +331,11 @@ def run_b200(args, rank, world, local):
         "gpu_launches": int(launches),
         "roofline": {"bound": "fp64_simt", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": (achieved_tf / fp64_peak) if achieved_tf else None, "traffic": None,
-                     "kernel": "k_sweep (threshold sweeps, both orientations, + CRP sweep)",
-                     "note": "algorithmic 26 flop/cell counted ONCE although the path sweeps each pair three times; "
-                             "peak = 148 SM x 64 FP64 lanes x 2 x sm_max_mhz (derived: MEASURED_PEAKS.json has no FP64 figure)"},
+                     "kernel": "k_sweep5 / k_sweep4 (separator sweep of one orientation + CRP sweep of the other)",
+                     "note": "algorithmic 26 flop/cell counted ONCE although every cell is computed twice (once per "
+                             "orientation); peak = 148 SM x 64 FP64 lanes x 2 x sm_max_mhz (derived; measured "
+                             "37.0 TFLOP/s by profiles/exp/ubench/fp64_lat.cu; MEASURED_PEAKS.json has no FP64 figure); "
+                             "the path is FP64-SIMT bound, not HBM or tensor bound (see roofline_hbm)"},
         "roofline_hbm": {"bound": "hbm", "achieved": (my_bytes / sweep_s / 1e9) if sweep_s > 0 else None, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (my_bytes / sweep_s / 1e9 / hbm_peak) if sweep_s > 0 else None,
                          "note": "compulsory bytes only (both songs' frames + scores); the path is compute-bound by design, "

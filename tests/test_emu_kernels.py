@@ -65,3 +65,23 @@ def test_emu_dp_multiblock(ctx):
         q, d = dp.qmax_dmax_serra09(B)
         assert (out[b, 0], out[b, 1]) == (q, d)
         assert pc.sw_close(out[b, 2], dp.sw_score(B))
+
+
+def test_emu_integer_key_sweeps(ctx):
+    """gen 4 / gen 5 kernel sources under emulation: several warps per row (halo columns), 8 compute
+    warps (the 512-thread CTA), inflated safety gap (float64 fallback path), other windows."""
+    songs, _ = synth.make_song_set("covers80", seed=33, n_songs=5, length_range=(60, 200))
+    songs += synth.make_song_set("covers80", seed=34, n_songs=2, length_range=(500, 560))[0]
+    pairs = np.array([(0, 1), (1, 2), (2, 3), (3, 4), (4, 0), (5, 6), (6, 2)], np.int32)
+    try:
+        for gen in (4, 5):
+            ctx.set_option("sweep_gen", gen)
+            for gap in (2, 4096):
+                ctx.set_option("gap_units", gap)
+                n, tied = pc.check_against_oracle(ctx, songs, pairs, m=9, kappa=0.095, flags=0)
+                assert n == len(pairs) and tied == 0
+        ctx.set_option("gap_units", 2)
+        pc.check_against_oracle(ctx, songs, pairs[:4], m=5, kappa=0.1, flags=_native.FLAG_NO_SWAP)
+    finally:
+        ctx.set_option("sweep_gen", 5)
+        ctx.set_option("gap_units", 2)

@@ -98,3 +98,53 @@ def test_errors(ctx):
         ctx.serra09_pairs(np.array([[0, 7]], np.int32))
     with pytest.raises(_native.AcossError):
         ctx.serra09_pairs(np.array([[0, 1]], np.int32), kappa=0.0)
+
+
+def test_sweep_generations_agree_and_exact_path(ctx):
+    """The integer-key sweeps (gen 4: phase-alternating, gen 5: warp-specialised) against the
+    float64-selection sweep (gen 2) and the oracle; then with the safety gap G inflated so that
+    many rows take the float64 fallback (flagged separators, band patches) instead of the
+    integer compare: the CRP must not move."""
+    songs, _ = synth.make_song_set("covers80", seed=44, n_songs=10, length_range=(130, 900))
+    rng = np.random.default_rng(2)
+    pairs = rng.integers(0, len(songs), size=(40, 2)).astype(np.int32)
+    pairs = pairs[pairs[:, 0] != pairs[:, 1]][:24]
+    ctx.upload_songs(songs)
+    try:
+        ctx.set_option("sweep_gen", 2)
+        base = ctx.serra09_pairs(pairs, want_crp=True)
+        for gen in (4, 5):
+            for gap in (2, 256, 1 << 14, 1 << 18):
+                ctx.set_option("sweep_gen", gen)
+                ctx.set_option("gap_units", gap)
+                r = ctx.serra09_pairs(pairs, want_crp=True)
+                where = "gen %d gap %d" % (gen, gap)
+                assert np.array_equal(r["oti"], base["oti"]), where
+                for a, b in zip(r["crp"], base["crp"]):
+                    assert np.array_equal(a, b), where + ": %d CRP bits differ" % int((a != b).sum())
+                assert np.array_equal(r["qmax_raw"], base["qmax_raw"]) and np.array_equal(r["dmax_raw"], base["dmax_raw"]), where
+    finally:
+        ctx.set_option("sweep_gen", 5)
+        ctx.set_option("gap_units", 2)
+    # and the default configuration against the oracle on the same pairs
+    n, tied = pc.check_against_oracle(ctx, songs, pairs[:10], flags=_native.FLAG_NO_SWAP)
+    assert tied <= 1
+
+
+def test_generations_agree_at_full_size(ctx):
+    # whatisacover-shaped lengths, 3000 pairs: the three sweep generations must give identical maxima
+    songs, _ = synth.make_song_set("whatisacover", seed=10000, n_songs=300)
+    rng = np.random.default_rng(7)
+    pairs = rng.integers(0, len(songs), size=(3200, 2)).astype(np.int32)
+    pairs = pairs[pairs[:, 0] != pairs[:, 1]][:3000]
+    ctx.upload_songs(songs)
+    out = {}
+    try:
+        for gen in (2, 4, 5):
+            ctx.set_option("sweep_gen", gen)
+            out[gen] = ctx.serra09_pairs(pairs)
+    finally:
+        ctx.set_option("sweep_gen", 5)
+    for gen in (4, 5):
+        assert np.array_equal(out[gen]["qmax_raw"], out[2]["qmax_raw"]), gen
+        assert np.array_equal(out[gen]["dmax_raw"], out[2]["dmax_raw"]), gen
