@@ -22,6 +22,7 @@
 #include "kernels_sweep3.cuh"
 #include "kernels_sweep4.cuh"
 #include "kernels_sweep5.cuh"
+#include "kernels_sweep6.cuh"
 
 #ifdef ACOSS_EMU
 #define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
@@ -113,6 +114,8 @@ int neighbours(double kappa, int n) {
 struct acoss_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;  // side stream for the few long-song sweeps (general kernels), higher priority
+    cudaEvent_t ev_prep = nullptr, ev_side = nullptr;
     int sm_count = 0;
     int max_smem = 0;
     // songs
@@ -135,11 +138,14 @@ struct acoss_ctx {
     int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
                                  // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
     int opt_chunk_pairs = 1 << 18;
-    int opt_sweep_gen = 5;         // 5: warp-specialised integer-key sweep (kernels_sweep5.cuh, default; falls back
+    int opt_sweep_gen = 6;         // 6 (default): DMMA sweep (kernels_sweep6.cuh) for every orientation whose column
+                                   // song has <= 631 frames (m = 9, 12 bins), the rest as 5;
+                                   // 5: warp-specialised integer-key sweep (kernels_sweep5.cuh; falls back
                                    // to 4 for windows other than 9 and column songs over 960 frames);
                                    // 4: integer-key sweep (kernels_sweep4.cuh); 2: float64-selection sweep
                                    // (kernels_sweep2.cuh); 3: warp-specialised variant of 2 (kernels_sweep3.cuh)
     int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
+    int opt_single_stream = 0;     // 1: no side stream (profiling / debugging)
     uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
     // accounting
     int64_t launches = 0;
@@ -153,13 +159,15 @@ namespace {
 constexpr int64_t kMaxChunkSepDoubles = (int64_t)1 << 28;  // 2 GiB
 constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
 constexpr int64_t kMaxChunkNbBytes = (int64_t)6 << 30;     // 6 GiB of nibble-byte CRPs (gen 4)
-constexpr int kCounterSlots = 64;
+constexpr int kCounterSlots = 96;
+constexpr int kG6Buckets = kS6Buckets;  // gen-6 launch buckets: CTAs of 128, 256, 512, 640 threads
 constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) threads, up to 128 * (b + 1) columns
 
 struct ItemLists {
     std::vector<uint32_t> fast0[kFastBuckets], fast2[kFastBuckets];  // fast sweep: separators / separators + CRP
     std::vector<uint32_t> wide0, wide1;                              // general sweep (long songs): MODE 0 / MODE 1
     std::vector<uint32_t> g4_0[kFastBuckets], g4_2[kFastBuckets];    // gen-4 sweep: separators / CRP
+    std::vector<uint32_t> g6_0[kS6Buckets], g6_2[kS6Buckets];  // gen-6 (DMMA) sweep by CTA size
     std::vector<uint32_t> g5_0[2], g5_2[2];                          // gen-5 sweep, 4 / 8 compute warps
     std::vector<uint32_t> g4_pack;                                   // pairs whose nibble CRP needs packing
     std::vector<uint32_t> dp4, dp8, dp16;
@@ -360,6 +368,46 @@ int launch_sweep5(acoss_ctx* c, const uint32_t* d_items, int n_items, int nwg, i
     return ACOSS_OK;
 }
 
+template <int MODE>
+int launch_sweep6(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter, uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    int threads = 0;
+    void (*kfn)(Sweep4Args) = nullptr;
+    switch (bucket) {
+        case 0: kfn = k_sweep6<MODE, 9, 128>; threads = 128; break;
+        case 1: kfn = k_sweep6<MODE, 9, 256>; threads = 256; break;
+        case 2: kfn = k_sweep6<MODE, 9, 512>; threads = 512; break;
+        case 3: kfn = k_sweep6<MODE, 9, 640>; threads = 640; break;
+        default: return fail(ACOSS_ERR_ARG, "k_sweep6: no kernel for bucket %d", bucket);
+    }
+    const size_t smem = (size_t)s6_layout(threads, 12).total;
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, threads, smem));
+    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep6 cannot be resident (threads %d, smem %zu B)", threads, smem);
+    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
+    Sweep4Args A;
+    memset(&A, 0, sizeof(A));
+    A.frames = c->frames.as<double>();
+    A.wnorm = c->wnorm.as<double>();
+    A.norms = c->norms.as<double>();
+    A.offs = c->offs.as<int64_t>();
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.counter = d_counter;
+    A.sepk = c->sepk.as<int32_t>();
+    A.sepx = c->sepx.as<double>();
+    A.nb = c->nb.as<uint8_t>();
+    A.m = m;
+    A.gap = c->opt_gap;
+    A.flags = flags;
+    ACOSS_LAUNCH(kfn, grid, threads, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
 template <int CPL>
 int launch_dp(acoss_ctx* c, const uint32_t* d_items, int n_items, uint32_t flags, float* q, float* d, float* sw) {
     if (n_items <= 0) return ACOSS_OK;
@@ -462,15 +510,25 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             if (gen4_ok && std::max(w.Li, w.Lj) <= s4_max_cols(m)) {
                 // gen 4: both orientations through the integer-key sweep (a warp contributes own4 columns)
                 const int own4 = s4_own_cols(m);
-                const bool g5 = c->opt_sweep_gen == 5 && m == 9;  // the warp-specialised kernels are built for m = 9
+                const bool g5 = c->opt_sweep_gen >= 5 && m == 9;  // the warp-specialised kernels are built for m = 9
                 const int b0 = (Lc_of(other) - 1) / own4, b2 = (Lc_of(dpo) - 1) / own4;  // compute warps needed - 1
+                // gen 6 (DMMA) per orientation where the column song fits its largest CTA
+                const bool g6 = c->opt_sweep_gen >= 6 && m == 9 &&
+                                (size_t)s6_layout(512, BINS).total <= (size_t)c->max_smem - 1024;
+                auto use6 = [&](int Lc) { return g6 && Lc <= kS6MaxThreads - kS6Pad; };
                 if (!(nonmutual && dpo == 0)) {
-                    if (g5 && b0 < 8)
+                    if (use6(Lc_of(other)))
+                        L.g6_0[s6_bucket_of(s6_threads_for(Lc_of(other)))].push_back((uint32_t)p * 2 + other);
+                    else if (g5 && b0 < 8)
                         L.g5_0[b0 / 4].push_back((uint32_t)p * 2 + other);
                     else
                         L.g4_0[b0].push_back((uint32_t)p * 2 + other);
                 }
-                if (g5 && b2 < 8) {
+                if (use6(Lc_of(dpo))) {
+                    const int t2 = s6_threads_for(Lc_of(dpo));
+                    L.g6_2[s6_bucket_of(t2)].push_back((uint32_t)p);
+                    w.nb_stride = t2 / 4;
+                } else if (g5 && b2 < 8) {
                     L.g5_2[b2 / 4].push_back((uint32_t)p);
                     w.nb_stride = 128 * (b2 / 4 + 1);
                 } else {
@@ -528,6 +586,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     for (int b = 0; b < kFastBuckets; ++b)
         n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
     for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
+    for (int b = 0; b < kG6Buckets; ++b) n_items += L.g6_0[b].size() + L.g6_2[b].size();
     CU(c->items.reserve(std::max<size_t>(n_items, 1) * sizeof(uint32_t)));
     // stage: [PairWork...][items...]
     const size_t pw_bytes = (size_t)n * sizeof(PairWork);
@@ -535,7 +594,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     memcpy(c->h_stage.p, W.data(), pw_bytes);
     uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_stage.as<char>() + pw_bytes);
     size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16, pos = 0;
-    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2];
+    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
     auto put = [&](const std::vector<uint32_t>& v) {
         size_t at = pos;
         if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
@@ -554,6 +613,8 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     o_g4pack = put(L.g4_pack);
     for (int b = 0; b < 2; ++b) o_g50[b] = put(L.g5_0[b]);
     for (int b = 0; b < 2; ++b) o_g52[b] = put(L.g5_2[b]);
+    for (int b = 0; b < kG6Buckets; ++b) o_g60[b] = put(L.g6_0[b]);
+    for (int b = 0; b < kG6Buckets; ++b) o_g62[b] = put(L.g6_2[b]);
     CU(cudaMemcpyAsync(c->pairs.p, c->h_stage.p, pw_bytes, cudaMemcpyHostToDevice, c->stream));
     if (n_items)
         CU(cudaMemcpyAsync(c->items.p, hi, n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
@@ -590,15 +651,42 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         CU(cudaGetLastError());
     }
     CU(cudaEventRecord(c->ev[1], c->stream));
-    // largest buckets first: their CTAs are the long ones
+    // Pairs with a song beyond the integer-key sweeps' reach go through the general kernels: few items,
+    // each a long CTA.  Launched alone they leave most SMs idle (profiles/r01_g: 27 % of a step), so
+    // they run on a second, higher-priority stream, first, and the persistent CTAs of the main sweeps
+    // take the SMs that are left.  The two families never share a pair.
+    bool side_work = !L.wide0.empty() || !L.wide1.empty(), main_work = !L.g4_pack.empty();
+    for (int b = 0; b < kFastBuckets; ++b) side_work = side_work || !L.fast0[b].empty() || !L.fast2[b].empty();
+    const bool side = side_work && main_work && !c->opt_single_stream;
+    {
+        struct StreamSwap {
+            acoss_ctx* c;
+            cudaStream_t keep;
+            ~StreamSwap() { c->stream = keep; }
+        } swap{c, c->stream};
+        if (side) {
+            CU(cudaEventRecord(c->ev_prep, c->stream));
+            CU(cudaStreamWaitEvent(c->stream2, c->ev_prep, 0));
+            c->stream = c->stream2;
+        }
+        // largest buckets first: their CTAs are the long ones
+        if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
+        for (int b = kFastBuckets - 1; b >= 0; --b)
+            if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+        if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
+        for (int b = kFastBuckets - 1; b >= 0; --b)
+            if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 2> : launch_sweep_ws<BINS, 2>)(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
+        if (side) CU(cudaEventRecord(c->ev_side, c->stream2));
+    }
+    for (int b = kG6Buckets - 1; b >= 0; --b)
+        if (BINS == 12 && (rc = launch_sweep6<0>(c, d_items + o_g60[b], (int)L.g6_0[b].size(), b, m, d_cnt + 64 + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep5<0>(c, d_items + o_g50[b], (int)L.g5_0[b].size(), b + 1, m, d_cnt + 56 + b, flags))) return rc;
     for (int b = kFastBuckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
-    for (int b = kFastBuckets - 1; b >= 0; --b)
-        if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
-    if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
+    for (int b = kG6Buckets - 1; b >= 0; --b)
+        if (BINS == 12 && (rc = launch_sweep6<2>(c, d_items + o_g62[b], (int)L.g6_2[b].size(), b, m, d_cnt + 64 + kG6Buckets + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep5<2>(c, d_items + o_g52[b], (int)L.g5_2[b].size(), b + 1, m, d_cnt + 58 + b, flags))) return rc;
     for (int b = kFastBuckets - 1; b >= 0; --b)
@@ -610,9 +698,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         c->launches++;
         CU(cudaGetLastError());
     }
-    for (int b = kFastBuckets - 1; b >= 0; --b)
-        if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 2> : launch_sweep_ws<BINS, 2>)(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
-    if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
+    if (side) CU(cudaStreamWaitEvent(c->stream, c->ev_side, 0));
     CU(cudaEventRecord(c->ev[3], c->stream));
     if ((rc = run_dp_lists(c, L, d_items, o_dp4, o_dp8, o_dp16, flags))) return rc;
     CU(cudaEventRecord(c->ev[4], c->stream));
@@ -686,6 +772,13 @@ int acoss_create(acoss_ctx** out, int device) {
     acoss_ctx* c = new acoss_ctx();
     c->device = device;
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    {
+        int prio_lo = 0, prio_hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        CU(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio_hi));
+        CU(cudaEventCreateWithFlags(&c->ev_prep, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming));
+    }
     CU(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
     CU(cudaDeviceGetAttribute(&c->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
     for (int i = 0; i < 5; ++i) CU(cudaEventCreate(&c->ev[i]));
@@ -697,6 +790,7 @@ int acoss_destroy(acoss_ctx* c) {
     if (!c) return ACOSS_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->stream2) cudaStreamSynchronize(c->stream2);
     DevBuf* bufs[] = {&c->frames, &c->norms, &c->offs, &c->gchroma, &c->pairs, &c->items, &c->counters,
                       &c->seps, &c->crp, &c->bnd, &c->qout, &c->dout, &c->swout, &c->otiout, &c->gscratch,
                       &c->dense_in, &c->dense_desc, &c->dense_starts,
@@ -705,6 +799,9 @@ int acoss_destroy(acoss_ctx* c) {
     c->h_stage.release();
     for (int i = 0; i < 5; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->ev_prep) cudaEventDestroy(c->ev_prep);
+    if (c->ev_side) cudaEventDestroy(c->ev_side);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return ACOSS_OK;
@@ -1038,11 +1135,13 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
     else if (n == "force_gscratch")
         c->opt_force_gscratch = value != 0;
     else if (n == "sweep_gen") {
-        if (value < 2 || value > 5) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2, 3, 4 or 5");
+        if (value < 2 || value > 6) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2 .. 6");
         c->opt_sweep_gen = (int)value;
     } else if (n == "gap_units") {
         if (value < 2 || value > (1 << 24)) return fail(ACOSS_ERR_ARG, "gap_units must be in [2, 2^24]");
         c->opt_gap = (int)value;
+    } else if (n == "single_stream") {
+        c->opt_single_stream = value ? 1 : 0;
     } else if (n == "debug_flags")
         c->opt_debug_flags = (uint32_t)value;
     else if (n == "dp_max_cpl") {

@@ -50,6 +50,7 @@ constexpr int32_t kKeyInf = 0x7fffffff;
 struct Sweep4Args {
     const double* frames;   // [total_frames][BINS]
     const double* wnorm;    // [total_frames] windowed squared norms: sum of the m frames ending here
+    const double* norms;    // [total_frames] squared norms of the frames (gen 6)
     const int64_t* offs;
     const PairWork* pairs;
     const uint32_t* items;  // MODE 0: pair*2 + orientation; MODE 2: pair
@@ -202,18 +203,18 @@ struct S4Keys<0> {
 // number of keys <= t (keys and t in [-1, 2^31): the sign of t - key says key > t)
 template <class K>
 __device__ __forceinline__ int s4_count(const K& keys, int t, int lane) {
-    unsigned s = 0;
+    unsigned s0 = 0, s1 = 0, s2 = 0, s3 = 0;  // four independent chains
     const int nq = keys.nq();
 #pragma unroll
     for (int q = 0; q < nq; ++q) {
         const uint4 v = keys.get(q);
-        s += (unsigned)(t - (int)v.x) >> 31;
-        s += (unsigned)(t - (int)v.y) >> 31;
-        s += (unsigned)(t - (int)v.z) >> 31;
-        s += (unsigned)(t - (int)v.w) >> 31;
+        s0 += (unsigned)(t - (int)v.x) >> 31;
+        s1 += (unsigned)(t - (int)v.y) >> 31;
+        s2 += (unsigned)(t - (int)v.z) >> 31;
+        s3 += (unsigned)(t - (int)v.w) >> 31;
     }
     (void)lane;
-    return 128 * nq - __reduce_add_sync(kFullMask, (int)s);
+    return 128 * nq - __reduce_add_sync(kFullMask, (int)((s0 + s1) + (s2 + s3)));
 }
 
 // The `need` smallest values of f(key) where f(key) = key - base (UP) or base - key (!UP); keys on
@@ -224,25 +225,28 @@ __device__ __forceinline__ int s4_count(const K& keys, int t, int lane) {
 template <bool UP, class K>
 __device__ __forceinline__ bool s4_walk(const K& keys, unsigned base, int need, int lane, unsigned& o_prev,
                                         unsigned& o_last) {
-    unsigned m1 = 0xffffffffu, m2 = 0xffffffffu;
+    // two independent (smallest, second smallest) chains, merged at the end
+    unsigned a1 = 0xffffffffu, a2 = 0xffffffffu, b1 = 0xffffffffu, b2 = 0xffffffffu;
     const int nq = keys.nq();
 #pragma unroll
     for (int q = 0; q < nq; ++q) {
         const uint4 v = keys.get(q);
-        unsigned x;
+        unsigned x, y;
         x = UP ? (v.x - base) : (base - v.x);
-        m2 = s4_umin(m2, s4_umax(m1, x));
-        m1 = s4_umin(m1, x);
-        x = UP ? (v.y - base) : (base - v.y);
-        m2 = s4_umin(m2, s4_umax(m1, x));
-        m1 = s4_umin(m1, x);
+        y = UP ? (v.y - base) : (base - v.y);
+        a2 = s4_umin(a2, s4_umax(a1, x));
+        a1 = s4_umin(a1, x);
+        b2 = s4_umin(b2, s4_umax(b1, y));
+        b1 = s4_umin(b1, y);
         x = UP ? (v.z - base) : (base - v.z);
-        m2 = s4_umin(m2, s4_umax(m1, x));
-        m1 = s4_umin(m1, x);
-        x = UP ? (v.w - base) : (base - v.w);
-        m2 = s4_umin(m2, s4_umax(m1, x));
-        m1 = s4_umin(m1, x);
+        y = UP ? (v.w - base) : (base - v.w);
+        a2 = s4_umin(a2, s4_umax(a1, x));
+        a1 = s4_umin(a1, x);
+        b2 = s4_umin(b2, s4_umax(b1, y));
+        b1 = s4_umin(b1, y);
     }
+    unsigned m1 = s4_umin(a1, b1);
+    unsigned m2 = s4_umin(s4_umax(a1, b1), s4_umin(a2, b2));
     int popped = 0;
     bool exhausted_early = false;
     o_prev = 0xffffffffu;
@@ -283,6 +287,7 @@ __device__ __forceinline__ void s4_boundary(const K& keys, int t, int& below, in
 
 struct S4Sel {
     float spacing;  // key units per rank around the separator
+    float scale;    // running estimate of (k-th key - row minimum), 0 = none yet (histogram selection)
 };
 
 // k-th and (k+1)-th smallest key of the strip row (1 <= k < nvalid; invalid positions hold
@@ -423,6 +428,125 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
     st.spacing = spacing;
 }
 
+// A first threshold from the row's own keys (no history needed): every lane finds the second
+// smallest of its keys; the k-th key of the row is close to the jrank-th smallest of those 32
+// values, where jrank = 32 P(a lane holds at least two of the k smallest) - 1 (s4_est_rank).
+// On the benchmark's rows the count at this threshold is within 6 ranks of k for ~85 % of the
+// rows, against ~15 % for the separator of a row 8-16 rows earlier.  Returns kKeyInf when there
+// is no such value.
+template <class K>
+__device__ __forceinline__ int s4_estimate(const K& keys, int jrank, int lane) {
+    unsigned a1 = 0xffffffffu, a2 = 0xffffffffu, b1 = 0xffffffffu, b2 = 0xffffffffu;
+    const int nq = keys.nq();
+#pragma unroll
+    for (int q = 0; q < nq; ++q) {
+        const uint4 v = keys.get(q);
+        a2 = s4_umin(a2, s4_umax(a1, v.x));
+        a1 = s4_umin(a1, v.x);
+        b2 = s4_umin(b2, s4_umax(b1, v.y));
+        b1 = s4_umin(b1, v.y);
+        a2 = s4_umin(a2, s4_umax(a1, v.z));
+        a1 = s4_umin(a1, v.z);
+        b2 = s4_umin(b2, s4_umax(b1, v.w));
+        b1 = s4_umin(b1, v.w);
+    }
+    const unsigned m2 = s4_umin(s4_umax(a1, b1), s4_umin(a2, b2));
+    int rank = 0;
+#pragma unroll
+    for (int l = 0; l < 32; ++l) {
+        const unsigned o = __shfl_sync(kFullMask, m2, l);
+        rank += (o < m2 || (o == m2 && l < lane)) ? 1 : 0;
+    }
+    const unsigned hit = __ballot_sync(kFullMask, rank == jrank);
+    const unsigned g = __shfl_sync(kFullMask, m2, __ffs((int)hit) - 1);
+    return (g >= (unsigned)kKeyInf) ? kKeyInf : (int)g;
+}
+// 0-based rank to use with s4_estimate for the k-th of nvalid keys spread over 32 lanes
+__device__ __forceinline__ int s4_est_rank(int k, int nvalid) {
+    const float n = (float)nvalid * (1.0f / 32.0f), p = (float)k / (float)nvalid;
+    const float q1 = exp2f((n - 1.0f) * log2f(1.0f - p));  // (1-p)^(n-1)
+    const float P2 = 1.0f - q1 * (1.0f - p) - n * p * q1;  // P(Binomial(n, p) >= 2)
+    int j = (int)(32.0f * P2 + 0.5f) - 1;
+    return j < 0 ? 0 : (j > 31 ? 31 : j);
+}
+
+// Histogram selection (no guess needed): 64 bins of width 2^sh above the row minimum, sized from
+// the running estimate `scale` of (k-th key - minimum) so that the k-th key is expected around bin
+// 16..32; an inclusive scan over the bin counts finds the bin holding rank k and the exact count
+// below it, and a candidate walk from that bin's lower edge pops the few keys up to rank k + 1.
+// Over-full bins are refined with a second (third) histogram inside the bin.  Returns false when
+// the k-th key lies beyond the 64 bins or the walk ran out of per-lane candidates: the caller
+// then uses s4_select, which is exact for any input.  hist_s: 64 ints of per-row scratch.
+template <class K>
+__device__ __forceinline__ bool s4_select_hist(const K& keys, int k, float scale, int* hist_s, int lane, int& vk,
+                                               int& vk1, unsigned& row_min) {
+    const int nq = keys.nq();
+    unsigned mn = 0xffffffffu;
+#pragma unroll
+    for (int q = 0; q < nq; ++q) {
+        const uint4 v = keys.get(q);
+        mn = s4_umin(mn, s4_umin(s4_umin(v.x, v.y), s4_umin(v.z, v.w)));
+    }
+    mn = __reduce_min_sync(kFullMask, mn);
+    row_min = mn;
+    if (!(scale >= 1.0f)) return false;
+    int sci = (scale < 1.0e9f) ? (int)scale : 1000000000;
+    if (sci < 16) sci = 16;
+    int sh = 27 - __clz(sci);  // sci >> sh in [16, 32)
+    unsigned base = mn;
+    int kk = k;
+    for (int level = 0; level < 3; ++level) {
+        hist_s[lane] = 0;
+        hist_s[lane + 32] = 0;
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < nq; ++q) {
+            const uint4 v = keys.get(q);
+            const unsigned b0 = (v.x - base) >> sh, b1 = (v.y - base) >> sh, b2 = (v.z - base) >> sh, b3 = (v.w - base) >> sh;
+            if (b0 < 64u) atomicAdd(&hist_s[b0], 1);
+            if (b1 < 64u) atomicAdd(&hist_s[b1], 1);
+            if (b2 < 64u) atomicAdd(&hist_s[b2], 1);
+            if (b3 < 64u) atomicAdd(&hist_s[b3], 1);
+        }
+        __syncwarp();
+        const int h0 = hist_s[2 * lane], h1 = hist_s[2 * lane + 1];
+        int c = h0 + h1;  // inclusive scan over lanes
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(kFullMask, c, d);
+            if (lane >= d) c += o;
+        }
+        __syncwarp();
+        const unsigned hit = __ballot_sync(kFullMask, c >= kk);
+        if (hit == 0u) return false;  // rank k lies beyond the bins
+        const int ls = __ffs((int)hit) - 1;
+        const int excl = c - h0 - h1;
+        const int first = (excl + h0 >= kk) ? 0 : 1;
+        const int binl = 2 * lane + first;
+        const int belowl = first ? excl + h0 : excl;
+        const int popl = first ? h1 : h0;
+        const int bin = __shfl_sync(kFullMask, binl, ls);
+        const int below = __shfl_sync(kFullMask, belowl, ls);
+        const int pop = __shfl_sync(kFullMask, popl, ls);
+        const int need = kk - below;  // 1 .. pop
+        const unsigned edge = base + ((unsigned)bin << sh);
+        if (need + 1 <= kS4EMax + 1) {
+            unsigned oa, ob;
+            const bool ok = s4_walk<true>(keys, edge, need + 1, lane, oa, ob);
+            if (!ok || oa >= 0x80000000u) return false;
+            vk = (int)(edge + oa);
+            vk1 = (ob >= 0x80000000u) ? kKeyInf : (int)(edge + ob);
+            return true;
+        }
+        // too many keys between the bin's edge and rank k: refine inside the bin
+        if (sh == 0 || pop < need) return false;
+        base = edge;
+        kk = need;
+        sh = (sh > 6) ? sh - 6 : 0;
+    }
+    return false;
+}
+
 // Unsafe row: the k-th and (k+1)-th keys are closer than 2G.  Collect the cells whose key lies
 // within 2 units of them, evaluate those in float64 (canonical orientation) and rank them.
 // Returns true and (sepx, n_cand, in-mask over candidate slots) when resolved; false when the
@@ -488,6 +612,9 @@ __device__ __noinline__ bool s4_resolve_unsafe(const uint4* __restrict__ row4, i
 struct S4RowArgs {
     const uint4* row4;   // the strip row (nq * 32 quads)
     int nq, srow, nrows; // quads per lane, row within the strip, rows in the strip
+    int est_rank;        // >= 0: first threshold from s4_estimate with this rank; < 0: from the separator history
+    bool use_hist;       // histogram selection first (cand_s doubles as its 64-bin scratch)
+    int hist_back;       // the guess extrapolates from the strip's last row and the one hist_back rows before it
     int irow, lane;      // window index within the row song
     int kk, No, m, G, BANDW;
     bool use_row;
@@ -542,13 +669,32 @@ __device__ __forceinline__ void s4_resolve_row(const Sweep4Args& A, const S4Pair
         if (nh >= 1) {
             const int tl = hist[2 * (spar ^ 1)];
             g = tl;
-            if (nh >= 2) g += ((tl - hist[2 * (spar ^ 1) + 1]) * (warp + 1)) / 2;
+            if (nh >= 2) g += ((tl - hist[2 * (spar ^ 1) + 1]) * (warp + 1)) / (2 * R.hist_back);
         }
-        s4_select(keys, kk, No, g - kwx, nh >= 1, st, lane, vk, vk1);
+        bool have = false;
+        bool have_g = nh >= 1;
+        int t0 = g - kwx;
+        if (R.est_rank >= 0) {
+            const int ge = s4_estimate(keys, R.est_rank, lane);
+            if (ge < kKeyInf - 1) {
+                t0 = ge;
+                have_g = true;
+            }
+        }
+        if (R.use_hist) {
+            unsigned rmin;
+            have = s4_select_hist(keys, kk, st.scale, cand_s, lane, vk, vk1, rmin);
+            if (!have) s4_select(keys, kk, No, t0, have_g, st, lane, vk, vk1);
+            const float sc = (float)(unsigned)(vk - (int)rmin);
+            st.scale = (st.scale >= 1.0f) ? 0.5f * (st.scale + sc) : sc;
+            if (st.scale < 1.0f) st.scale = 1.0f;
+        } else {
+            s4_select(keys, kk, No, t0, have_g, st, lane, vk, vk1);
+        }
         if (lane == 0) {
             if (warp == nrows - 1) hist[2 * spar] = vk + kwx;
-            if (warp == nrows - 2) hist[2 * spar + 1] = vk + kwx;
-            if (warp == 0) misc[8 + spar] = nrows >= 2 ? 2 : 1;
+            if (warp == nrows - 1 - R.hist_back) hist[2 * spar + 1] = vk + kwx;
+            if (warp == 0) misc[8 + spar] = nrows > R.hist_back ? 2 : 1;
         }
         const int gap = vk1 - vk;
         if (gap >= 2 * G) {
@@ -972,6 +1118,9 @@ __global__ void ACOSS_MAXNREG4(168) k_sweep4(Sweep4Args A) {
                 ra.nq = NW;
                 ra.srow = warp;
                 ra.nrows = nrows;
+                ra.hist_back = 1;
+                ra.use_hist = false;
+                ra.est_rank = -1;
                 ra.irow = i - (nrows - 1) + warp;  // window index within the row song
                 ra.lane = lane;
                 ra.kk = kk;

@@ -354,6 +354,9 @@ __global__ void __launch_bounds__(256 * NWG, (NWG == 1 ? 2 : 1)) k_sweep5(Sweep4
                     ra.nq = NC;
                     ra.srow = sw;
                     ra.nrows = nrows;
+                    ra.hist_back = 1;
+                    ra.use_hist = false;
+                    ra.est_rank = -1;
                     ra.irow = s * NC + sw;
                     ra.lane = lane;
                     ra.kk = kk;

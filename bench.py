@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--cpu-pairs", type=int, default=0,
                     help="pairs of the CPU sample (0: 800 per core in the default arm = 15-25 s of CPU work, "
                          "150 per core and step in the reference arm)")
-    ap.add_argument("--sweep-gen", type=int, default=0, help="force a sweep generation (2, 4, 5); 0 = library default")
+    ap.add_argument("--sweep-gen", type=int, default=0, help="force a sweep generation (2 .. 6); 0 = library default")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 

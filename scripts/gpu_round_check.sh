@@ -9,8 +9,8 @@ timeout 300 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --pairs-per-s
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_r01.csv \
     python bench.py --steps 1 --warmup 1 --no-cpu-baseline --pairs-per-step 20000 > gpurun_out/ncu1.log 2>&1
 python profiles/exp/prof_target.py > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:"k_sweep5|k_dp|k_nb" -c 4 -o /tmp/prof_g5 \
+ncu --set full --clock-control none --import-source on -k regex:"k_sweep6|k_sweep5|k_dp" -c 6 -o /tmp/prof_g6 \
     python profiles/exp/prof_target.py > gpurun_out/ncu2.log 2>&1
-python profiles/ncu_summary.py /tmp/prof_g5.ncu-rep --lines 30 > gpurun_out/prof_g5_summary.txt 2>&1
-ncu -i /tmp/prof_g5.ncu-rep --page raw --csv > gpurun_out/prof_g5_raw.csv 2>/dev/null
-[ $(stat -c %s /tmp/prof_g5.ncu-rep) -lt 40000000 ] && cp /tmp/prof_g5.ncu-rep gpurun_out/
+python profiles/ncu_summary.py /tmp/prof_g6.ncu-rep --lines 30 > gpurun_out/prof_g6_summary.txt 2>&1
+ncu -i /tmp/prof_g6.ncu-rep --page raw --csv > gpurun_out/prof_g6_raw.csv 2>/dev/null
+[ $(stat -c %s /tmp/prof_g6.ncu-rep) -lt 40000000 ] && cp /tmp/prof_g6.ncu-rep gpurun_out/
