@@ -787,9 +787,12 @@ __device__ __forceinline__ void s4_resolve_row(const Sweep4Args& A, const S4Pair
             __syncwarp();
         }
         // ---- bits: nibble per (lane, quad), one byte per thread-quad of the row
-        uint8_t* out = A.nb + R.nb_off + (int64_t)irow * R.nb_stride;
+        uint8_t* out = A.nb + R.nb_off + (int64_t)irow * R.nb_stride + lane;
         const uint4* csk4 = reinterpret_cast<const uint4*>(csk_s);
-        for (int q = 0; q < NW; ++q) {
+        const bool generic = misc[10] != 0;
+        const int nqq = (NQ > 0) ? NQ : NW;  // compile-time trip count when the CTA size is
+#pragma unroll
+        for (int q = 0; q < nqq; ++q) {
             const int tq = lane + 32 * q;
             const uint4 kv = row4[tq];
             const uint4 cv = csk4[tq];
@@ -798,7 +801,7 @@ __device__ __forceinline__ void s4_resolve_row(const Sweep4Args& A, const S4Pair
             nib |= ((int)kv.y <= imin(thr, (int)cv.y - kwx)) ? 2u : 0u;
             nib |= ((int)kv.z <= imin(thr, (int)cv.z - kwx)) ? 4u : 0u;
             nib |= ((int)kv.w <= imin(thr, (int)cv.w - kwx)) ? 8u : 0u;
-            if (misc[10] != 0 && (int)(cv.x | cv.y | cv.z | cv.w) < 0) {
+            if (generic && (int)(cv.x | cv.y | cv.z | cv.w) < 0) {
                 // generic path (only when the item has more flagged columns than the patch list
                 // holds): a negative entry is a flagged column that is not in the list
                 const int kvv[4] = {(int)kv.x, (int)kv.y, (int)kv.z, (int)kv.w};
@@ -830,11 +833,13 @@ __device__ __forceinline__ void s4_resolve_row(const Sweep4Args& A, const S4Pair
                     if (colin && rowin) nib |= 1u << c;
                 }
             }
-            for (int p = 0; p < npatch; ++p) {
-                const int col = patch_cols[p];
-                if ((col >> 2) == tq) nib |= 1u << (col & 3);
+            if (npatch > 0) {
+                for (int p = 0; p < npatch; ++p) {
+                    const int col = patch_cols[p];
+                    if ((col >> 2) == tq) nib |= 1u << (col & 3);
+                }
             }
-            out[tq] = (uint8_t)nib;
+            out[32 * q] = (uint8_t)nib;
         }
     }
 

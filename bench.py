@@ -329,13 +329,17 @@ def run_b200(args, rank, world, local):
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": 1e3 * dt_e2e / args.steps},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "fp64_simt", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+        "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": (achieved_tf / fp64_peak) if achieved_tf else None, "traffic": None,
-                     "kernel": "k_sweep5 / k_sweep4 (separator sweep of one orientation + CRP sweep of the other)",
-                     "note": "algorithmic 26 flop/cell counted ONCE although every cell is computed twice (once per "
-                             "orientation); peak = 148 SM x 64 FP64 lanes x 2 x sm_max_mhz (derived; measured "
-                             "37.0 TFLOP/s by profiles/exp/ubench/fp64_lat.cu; MEASURED_PEAKS.json has no FP64 figure); "
-                             "the path is FP64-SIMT bound, not HBM or tensor bound (see roofline_hbm)"},
+                     "kernel": "k_sweep6 (FP64 tensor-core sweep: separators of one orientation + CRP of the other); "
+                               "k_sweep5 / k_sweep4 (FP64 SIMT) for column songs over 631 frames",
+                     "note": "FP64 roofline, NOT the bf16 figure of MEASURED_PEAKS.json (which has no FP64 entry): "
+                             "peak = 148 SM x 64 FP64 FMA/cycle x 2 x sm_max_mhz, the rate measured for both DMMA "
+                             "(mma.sync.m8n8k4.f64, profiles/exp/ubench/dmma_rate.cu: 16 cycles per instruction per SM "
+                             "sub-partition) and DFMA (profiles/exp/ubench/fp64_lat.cu); algorithmic 26 flop/cell counted "
+                             "ONCE although every cell is computed twice (once per orientation); achieved = flops of all "
+                             "sweep launches of the timed steps / their summed device time (CUDA events on the launching "
+                             "stream); the sweeps are bound by the integer selection, not by the FP64 pipe (DESIGN.md 7)"},
         "roofline_hbm": {"bound": "hbm", "achieved": (my_bytes / sweep_s / 1e9) if sweep_s > 0 else None, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (my_bytes / sweep_s / 1e9 / hbm_peak) if sweep_s > 0 else None,
                          "note": "compulsory bytes only (both songs' frames + scores); the path is compute-bound by design, "
