@@ -132,7 +132,13 @@ int acoss_qmax_dmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, floa
 int acoss_swconstrained(acoss_ctx* ctx, const uint8_t* S, int32_t N, int32_t M, float* result);
 
 /* Test / tuning knobs (results never depend on them): "force_wide_sweep" (0/1),
- * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "chunk_pairs" (pairs per internal chunk). */
+ * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "chunk_pairs" (pairs per internal chunk),
+ * "sweep_gen" (2 .. 6: which generation of the cross-similarity sweep runs where it applies;
+ * default 6 = FP64 tensor-core sweep for column songs of up to 631 frames, warp-specialised
+ * SIMT sweep up to 960, integer-key SIMT sweep up to 1320, general sweeps beyond),
+ * "gap_units" (2 .. 2^24: safety gap, in key units, below which a separator is re-decided in
+ * float64; larger values only move work to the exact path), "single_stream" (0/1: keep the
+ * long-song sweeps on the main stream), "debug_flags" (profiling experiments). */
 int acoss_set_option(acoss_ctx* ctx, const char* name, int64_t value);
 
 /* Counters for bench.py: kernels launched by this context since creation / last reset. */
