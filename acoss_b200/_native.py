@@ -42,6 +42,9 @@ SIGNATURES = {
                                            _c_i64p, _c_i32p]),
     "acoss_align_dense": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, _c_i64p, _c_i32p, _c_i32p,
                                          ctypes.c_int32, ctypes.c_double, ctypes.c_uint32, _c_f32p, _c_u32p, _c_i64p]),
+    "acoss_aggregate_songs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, _c_i64p, _c_i32p,
+                                             ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                             ctypes.c_void_p, _c_i64p, ctypes.c_void_p]),
     "acoss_dp_packed": (ctypes.c_int, [ctypes.c_void_p, _c_u32p, _c_i64p, _c_i32p, _c_i32p, ctypes.c_int32,
                                        ctypes.c_uint32, _c_f32p]),
     "acoss_qmax": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p]),
@@ -249,6 +252,42 @@ class Context:
                                         int(cols[b])))
             return out, crps
         return out
+
+    def aggregate_songs(self, arrays, fac=40, aggregate="median", layout="frames_x_bins", zero_nonfinite=False,
+                        want_gchroma=False):
+        """Block aggregation of full-rate features on the device (Serra09.load_features,
+        Serra09.py:101-110).  arrays: list of 2-D float32 or float64 arrays, all (n, bins)
+        ("frames_x_bins": hpcp / crema) or all (bins, n) ("bins_x_frames": mfcc_htk).  Returns a
+        list of (bins, ceil(n / fac)) arrays like librosa.util.sync(a.T or a, arange(0, n, fac))
+        and, with want_gchroma, the (n_songs, bins) global chroma (Serra09.py:24-28)."""
+        S = len(arrays)
+        dt = np.float64 if any(np.asarray(a).dtype == np.float64 for a in arrays) else np.float32
+        lay = 0 if layout == "frames_x_bins" else 1
+        bins = int(arrays[0].shape[1 if lay == 0 else 0]) if S else 0
+        nfr = np.array([a.shape[0 if lay == 0 else 1] for a in arrays], np.int32)
+        offs = np.zeros(S, np.int64)
+        if S > 1:
+            offs[1:] = np.cumsum(nfr[:-1].astype(np.int64))
+        flat = np.empty(max(int(nfr.astype(np.int64).sum()) * max(bins, 1), 1), dt)
+        for a, o, n in zip(arrays, offs, nfr):
+            a = np.ascontiguousarray(a, dtype=dt)
+            if a.shape[1 if lay == 0 else 0] != bins:
+                raise ValueError("all songs must have the same number of bins")
+            flat[o * bins:(o + int(n)) * bins] = a.reshape(-1)
+        L = (nfr.astype(np.int64) + fac - 1) // fac
+        ooffs = np.zeros(S, np.int64)
+        if S > 1:
+            ooffs[1:] = np.cumsum(L[:-1])
+        out = np.empty(max(int(L.sum()) * max(bins, 1), 1), dt)
+        g = np.empty((S, bins), dt) if want_gchroma else None
+        rc = self.lib.acoss_aggregate_songs(self._h, flat.ctypes.data_as(ctypes.c_void_p), F64 if dt == np.float64 else F32,
+                                            lay, _ptr(offs, _c_i64p), _ptr(nfr, _c_i32p), S, bins, int(fac),
+                                            0 if aggregate == "median" else 1, 1 if zero_nonfinite else 0,
+                                            out.ctypes.data_as(ctypes.c_void_p), _ptr(ooffs, _c_i64p),
+                                            None if g is None else g.ctypes.data_as(ctypes.c_void_p))
+        self._check(rc, "acoss_aggregate_songs")
+        res = [out[o * bins:(o + int(l)) * bins].reshape(int(l), bins).T for o, l in zip(ooffs, L)]
+        return (res, g) if want_gchroma else res
 
     def dp_packed(self, plots, flags=0, want_sw=False):
         """plots: list of uint8 (rows, cols) binary matrices.  Returns (B, 3) [qmax, dmax, sw]."""

@@ -23,6 +23,7 @@
 #include "kernels_sweep4.cuh"
 #include "kernels_sweep5.cuh"
 #include "kernels_sweep6.cuh"
+#include "kernels_feat.cuh"
 
 #ifdef ACOSS_EMU
 #define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
@@ -1125,6 +1126,116 @@ int acoss_swconstrained(acoss_ctx* c, const uint8_t* S, int32_t N, int32_t M, fl
     int rc = dp_unpacked(c, S, N, M, kFlagDmaxClean | kFlagWantSw, o);
     *result = o[2];
     return rc;
+}
+
+// ---------------------------------------------------------------- feature aggregation
+int acoss_aggregate_songs(acoss_ctx* c, const void* full, int dtype, int layout, const int64_t* offsets,
+                          const int32_t* nframes, int32_t n_songs, int32_t bins, int32_t fac, int32_t aggregate,
+                          int32_t zero_nonfinite, void* out, const int64_t* out_offsets, void* gchroma_out) {
+    if (!c) return fail(ACOSS_ERR_ARG, "context is null");
+    if (!full || !offsets || !nframes || !out || !out_offsets) return fail(ACOSS_ERR_ARG, "null argument");
+    if (dtype != ACOSS_F32 && dtype != ACOSS_F64) return fail(ACOSS_ERR_ARG, "dtype must be ACOSS_F32 or ACOSS_F64");
+    if (layout != 0 && layout != 1) return fail(ACOSS_ERR_ARG, "layout must be 0 (frames x bins) or 1 (bins x frames)");
+    if (aggregate != 0 && aggregate != 1) return fail(ACOSS_ERR_ARG, "aggregate must be 0 (median) or 1 (mean)");
+    if (bins < 1 || bins > 64) return fail(ACOSS_ERR_ARG, "bins must be in 1..64");
+    if (fac < 1 || fac > kFeatMaxFac) return fail(ACOSS_ERR_ARG, "fac must be in 1..%d", kFeatMaxFac);
+    if (gchroma_out && layout != 0) return fail(ACOSS_ERR_ARG, "the global chroma needs the frames x bins layout");
+    if (n_songs <= 0) return ACOSS_OK;
+    for (int s = 0; s < n_songs; ++s)
+        if (nframes[s] < 1) return fail(ACOSS_ERR_ARG, "song %d has no frames", s);
+    CU(cudaSetDevice(c->device));
+    const size_t es = dtype == ACOSS_F32 ? 4 : 8;
+    const size_t chunk_budget = (size_t)512 << 20;  // bytes of full-rate input per chunk
+    DevBuf d_in, d_out, d_meta, d_g;
+    struct Rel {
+        DevBuf *a, *b, *c2, *d;
+        ~Rel() { a->release(); b->release(); c2->release(); d->release(); }
+    } rel{&d_in, &d_out, &d_meta, &d_g};
+    int s0 = 0;
+    std::vector<int64_t> in_off, out_off;
+    while (s0 < n_songs) {
+        // ---- cut a chunk of consecutive songs
+        int s1 = s0;
+        size_t in_el = 0, out_el = 0;
+        in_off.clear();
+        out_off.clear();
+        while (s1 < n_songs && s1 - s0 < 32768) {
+            const size_t el = (size_t)nframes[s1] * bins;
+            if (s1 > s0 && (in_el + el) * es > chunk_budget) break;
+            in_off.push_back((int64_t)in_el);
+            out_off.push_back((int64_t)out_el);
+            in_el += el;
+            out_el += (size_t)((nframes[s1] + fac - 1) / fac) * bins;
+            ++s1;
+        }
+        const int ns = s1 - s0;
+        CU(d_in.reserve(in_el * es));
+        CU(d_out.reserve(out_el * es));
+        CU(d_meta.reserve((size_t)ns * (2 * sizeof(int64_t) + sizeof(int32_t)) + 64));
+        if (gchroma_out) CU(d_g.reserve((size_t)ns * bins * es));
+        // songs need not be contiguous on the host: one copy per song
+        int maxL = 0;
+        for (int s = s0; s < s1; ++s) {
+            CU(cudaMemcpyAsync(d_in.as<char>() + (size_t)in_off[s - s0] * es,
+                               reinterpret_cast<const char*>(full) + (size_t)offsets[s] * bins * es,
+                               (size_t)nframes[s] * bins * es, cudaMemcpyHostToDevice, c->stream));
+            maxL = std::max(maxL, (nframes[s] + fac - 1) / fac);
+        }
+        int64_t* m_in = d_meta.as<int64_t>();
+        int64_t* m_out = m_in + ns;
+        int32_t* m_n = reinterpret_cast<int32_t*>(m_out + ns);
+        CU(cudaMemcpyAsync(m_in, in_off.data(), (size_t)ns * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(m_out, out_off.data(), (size_t)ns * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(m_n, nframes + s0, (size_t)ns * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+        FeatArgs A;
+        A.in = d_in.p;
+        A.in_off = m_in;
+        A.nframes = m_n;
+        A.out = d_out.p;
+        A.out_off = m_out;
+        A.gchroma = gchroma_out ? d_g.p : nullptr;
+        A.n_songs = ns;
+        A.bins = bins;
+        A.fac = fac;
+        A.layout = layout;
+        A.aggregate = aggregate;
+        A.zero_nonfinite = zero_nonfinite;
+        A.blocks_per_song = (maxL * bins + 127) / 128;
+        const int64_t grid64 = (int64_t)A.blocks_per_song * ns;
+        if (grid64 > 0x7fffffffLL) return fail(ACOSS_ERR_ARG, "aggregation chunk too large");
+        const int grid = (int)grid64;
+        if (dtype == ACOSS_F32) {
+            auto kf = k_feat_aggregate<float>;
+            ACOSS_LAUNCH(kf, grid, 128, 0, c->stream, A);
+        } else {
+            auto kf = k_feat_aggregate<double>;
+            ACOSS_LAUNCH(kf, grid, 128, 0, c->stream, A);
+        }
+        c->launches++;
+        CU(cudaGetLastError());
+        if (gchroma_out) {
+            if (dtype == ACOSS_F32) {
+                auto kg = k_feat_gchroma<float>;
+                ACOSS_LAUNCH(kg, (ns + 3) / 4, 128, 0, c->stream, A);
+            } else {
+                auto kg = k_feat_gchroma<double>;
+                ACOSS_LAUNCH(kg, (ns + 3) / 4, 128, 0, c->stream, A);
+            }
+            c->launches++;
+            CU(cudaGetLastError());
+            CU(cudaMemcpyAsync(reinterpret_cast<char*>(gchroma_out) + (size_t)s0 * bins * es, d_g.p, (size_t)ns * bins * es,
+                               cudaMemcpyDeviceToHost, c->stream));
+        }
+        for (int s = s0; s < s1; ++s) {
+            const size_t L = (size_t)((nframes[s] + fac - 1) / fac);
+            CU(cudaMemcpyAsync(reinterpret_cast<char*>(out) + (size_t)out_offsets[s] * bins * es,
+                               d_out.as<char>() + (size_t)out_off[s - s0] * es, L * bins * es, cudaMemcpyDeviceToHost,
+                               c->stream));
+        }
+        CU(cudaStreamSynchronize(c->stream));
+        s0 = s1;
+    }
+    return ACOSS_OK;
 }
 
 int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {

@@ -62,6 +62,7 @@ class Serra09(CoverAlgorithm):
         self.device = device
         self.do_mfcc = do_mfcc
         self._ctx = {}        # 'chroma' / 'mfcc' -> (Context, song index -> arena slot)
+        self._feat_ctx = None # context used by load_features_batch
         self._packed = {}     # kind -> (song ids, packed host arena): what load_features cached, ready to upload
         self.last_stage_ms = None
         similarity_types = ["chroma_qmax", "chroma_dmax"]
@@ -97,6 +98,45 @@ class Serra09(CoverAlgorithm):
         self.all_feats[i] = ret
         return ret
 
+    def load_features_batch(self, ids, batch=256):
+        """load_features for many songs at once, the x40 aggregation and the global chroma done on
+        the device (acoss_aggregate_songs).  Same results as load_features, bit
+        for bit; songs that are already prepared or cached are skipped."""
+        todo = [int(i) for i in np.unique(np.asarray(ids, dtype=np.int64)) if int(i) not in self.all_feats]
+        raw = []
+        for i in todo:
+            feats = CoverAlgorithm.load_features(self, i)
+            if 'gchroma' in feats and 'chroma' in feats:
+                self.load_features(i)
+            else:
+                raw.append((i, feats))
+        if not raw:
+            return
+        if self._feat_ctx is None:
+            self._feat_ctx = _native.Context(self.device)
+        ctx = self._feat_ctx
+        for b0 in range(0, len(raw), batch):
+            part = raw[b0:b0 + batch]
+            chromas = [np.asarray(f[self.chroma_type]) for _, f in part]
+            for c in chromas:
+                if c.shape[1] not in [12, 24, 36]:   # global_chroma's check, Serra09.py:25-26
+                    raise IOError("Wrong axis for the input chroma array. Expected shape '(frame_size, bin_size)'")
+            agg, g = ctx.aggregate_songs(chromas, fac=self.downsample_fac, aggregate="median", want_gchroma=True)
+            mf = [None] * len(part)
+            have = [k for k, (_, f) in enumerate(part) if self.do_mfcc and 'mfcc_htk' in f]
+            if have:
+                res = ctx.aggregate_songs([np.asarray(part[k][1]['mfcc_htk']) for k in have], fac=self.downsample_fac,
+                                          aggregate="mean", layout="bins_x_frames", zero_nonfinite=True)
+                for k, r in zip(have, res):
+                    mf[k] = r
+            for k, (i, _) in enumerate(part):
+                chroma, mfcc = np.asfortranarray(agg[k]), mf[k]
+                if mfcc is not None:
+                    N = min(chroma.shape[1], mfcc.shape[1])      # Serra09.py:111-114
+                    chroma = chroma[:, 0:N]
+                    mfcc = np.asfortranarray(mfcc)[:, 0:N]
+                self.all_feats[i] = {'gchroma': g[k].copy(), 'chroma': chroma, 'mfcc': mfcc, 'ssms': None}
+
     # ------------------------------------------------------------------ device arena
     def _context_for(self, kind, song_ids):
         """Make sure every song in song_ids is in the device arena of `kind`; returns
@@ -115,6 +155,7 @@ class Serra09(CoverAlgorithm):
         if cached is not None and np.all(np.isin(need, cached[0])):
             need, packed = cached   # the cached host arena already covers these songs
         else:
+            self.load_features_batch(need)
             songs = []
             for i in need:
                 f = self.load_features(int(i))
@@ -183,6 +224,9 @@ class Serra09(CoverAlgorithm):
         for ctx, _ in self._ctx.values():
             ctx.close()
         self._ctx = {}
+        if self._feat_ctx is not None:
+            self._feat_ctx.close()
+            self._feat_ctx = None
 
 
 def main(argv=None):

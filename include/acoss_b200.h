@@ -131,6 +131,23 @@ int acoss_dmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, float* re
 int acoss_qmax_dmax(acoss_ctx* ctx, const uint8_t* S, int32_t M, int32_t N, float* qmax_result, float* dmax_result);
 int acoss_swconstrained(acoss_ctx* ctx, const uint8_t* S, int32_t N, int32_t M, float* result);
 
+/*
+ * The step before the path (Serra09.load_features, benchmarking/Serra09.py:96-114) on the
+ * device: block aggregation of full-rate features over `fac` frames, slices
+ * [fac*k, min(fac*(k+1), n)) as librosa.util.sync(data, arange(0, n, fac)) cuts them, with
+ * aggregate 0 = np.median (chroma, Serra09.py:104) or 1 = np.mean (mfcc, :110), in the input's
+ * precision and numpy's summation order; zero_nonfinite replaces NaN / Inf by 0 first
+ * (Serra09.py:107-109).  Song s has nframes[s] frames at `full` + offsets[s]*bins elements,
+ * layout 0 = frames x bins (hpcp / crema), 1 = bins x frames (mfcc_htk).  `out` receives
+ * ceil(nframes/fac) x bins per song, frames x bins (what acoss_upload_songs takes), at
+ * out + out_offsets[s]*bins elements.  gchroma_out (nullable, layout 0 only):
+ * [n_songs][bins] global chroma sum_t / max (Serra09.py:24-28), same dtype.  Host pointers.
+ */
+int acoss_aggregate_songs(acoss_ctx* ctx, const void* full, int dtype, int layout,
+                          const int64_t* offsets, const int32_t* nframes, int32_t n_songs,
+                          int32_t bins, int32_t fac, int32_t aggregate, int32_t zero_nonfinite,
+                          void* out, const int64_t* out_offsets, void* gchroma_out);
+
 /* Test / tuning knobs (results never depend on them): "force_wide_sweep" (0/1),
  * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "chunk_pairs" (pairs per internal chunk),
  * "sweep_gen" (2 .. 6: which generation of the cross-similarity sweep runs where it applies;

@@ -387,6 +387,8 @@ inline double __dadd_rn(double a, double b) { volatile double r = a + b; return 
 inline double __fma_rn(double a, double b, double c) { return std::fma(a, b, c); }
 inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
 inline float __fadd_rn(float a, float b) { volatile float r = a + b; return r; }
+inline float __fdiv_rn(float a, float b) { volatile float r = a / b; return r; }
+inline double __ddiv_rn(double a, double b) { volatile double r = a / b; return r; }
 inline float __fmul_rn(float a, float b) { volatile float r = a * b; return r; }
 inline float __fdividef(float a, float b) { return a / b; }
 inline int __double2int_rn(double v) { return (int)std::nearbyint(v); }

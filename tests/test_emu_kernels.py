@@ -85,3 +85,29 @@ def test_emu_integer_key_sweeps(ctx):
     finally:
         ctx.set_option("sweep_gen", 6)
         ctx.set_option("gap_units", 2)
+
+
+def test_emu_feature_aggregation(ctx):
+    """k_feat_aggregate / k_feat_gchroma under emulation against numpy (median, mean, global chroma)."""
+    from oracle import features_oracle as fo
+    rng = np.random.default_rng(3)
+    for dtype in (np.float32, np.float64):
+        songs = []
+        for n in (1, 7, 39, 40, 41, 80, 333):
+            a = rng.random((n, 12)).astype(dtype) ** 2
+            a[rng.random((n, 12)) < 0.05] = 0
+            songs.append(a)
+        agg, g = ctx.aggregate_songs(songs, fac=40, aggregate="median", want_gchroma=True)
+        for s, (a, got) in enumerate(zip(songs, agg)):
+            assert np.array_equal(got, fo.sync(a.T, 40, np.median)), (dtype, s)
+            assert np.array_equal(g[s], fo.global_chroma(a)), (dtype, s)
+    songs = []
+    for n in (3, 40, 47, 300):
+        a = (rng.standard_normal((13, n)) * 30).astype(np.float32)
+        a[0, 0] = np.nan
+        songs.append(a)
+    agg = ctx.aggregate_songs(songs, fac=40, aggregate="mean", layout="bins_x_frames", zero_nonfinite=True)
+    for a, got in zip(songs, agg):
+        m = np.array(a)
+        m[np.isnan(m)] = 0
+        assert np.array_equal(got, fo.sync(m, 40, np.mean))

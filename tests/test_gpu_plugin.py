@@ -77,3 +77,34 @@ def test_mfcc_similarity_types(tmp_path, monkeypatch):
                                     None, None, 9, 0.095, do_oti=False)
         assert sims["mfcc_qmax"][p] == r["qmax"] and sims["mfcc_dmax"][p] == r["dmax"]
     alg.close()
+
+
+def test_raw_features_are_aggregated_on_the_device(tmp_path, monkeypatch):
+    """Songs given as full-rate features (crema (n, 12) float64 + mfcc_htk (13, n) float32, the
+    fields of the reference's per-song files, extractors.py:43-54): load_features_batch (GPU) must
+    give exactly what load_features (numpy, Serra09.py:99-114 restated) gives, and the scores
+    computed from them must match."""
+    monkeypatch.chdir(tmp_path)
+    rng = np.random.default_rng(5)
+    raw = []
+    for s in range(6):
+        n = int(rng.integers(4000, 9000))
+        base = np.abs(rng.standard_normal((n // 50 + 2, 12))).repeat(50, axis=0)[:n]
+        crema = (base + 0.05 * rng.random((n, 12))).astype(np.float64)
+        mfcc = (rng.standard_normal((13, n)) * 20).astype(np.float32)
+        mfcc[3, 7] = np.nan
+        raw.append({"crema": crema, "mfcc_htk": mfcc, "label": "c%d" % (s // 2)})
+    a = Serra09(songs=raw, shortname="raw", do_memmaps=False, do_mfcc=True, cachedir="cache")
+    b = Serra09(songs=raw, shortname="raw2", do_memmaps=False, do_mfcc=True, cachedir="cache")
+    b.load_features_batch(np.arange(6))
+    for i in range(6):
+        fa, fb = a.load_features(i), b.all_feats[i]
+        assert np.array_equal(fa["gchroma"], fb["gchroma"])
+        assert fa["chroma"].dtype == fb["chroma"].dtype and np.array_equal(fa["chroma"], fb["chroma"])
+        assert fa["mfcc"].dtype == fb["mfcc"].dtype and np.array_equal(fa["mfcc"], fb["mfcc"])
+    idx = np.array([(0, 1), (2, 3), (0, 5)])
+    sa, sb = a.similarity(idx), b.similarity(idx)
+    for k in sa:
+        assert np.array_equal(sa[k], sb[k]), k
+    a.close()
+    b.close()
