@@ -1271,6 +1271,28 @@ void acoss_reset_counters(acoss_ctx* c) {
     if (c) c->launches = 0;
 }
 
+/* Profiling aid, not part of the drop-in surface: cycle counters of k_sweep6 (debug flag bit 26),
+ * summed over every warp: [0] stage 2, [1] selection, [2] stage 1, [3] barrier wait, [4] periods (per CTA),
+ * [5] items.  reset != 0 clears them. */
+int acoss_debug_sweep6_cycles(acoss_ctx* c, uint64_t out[8], int reset) {
+    if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
+#ifndef ACOSS_EMU
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    unsigned long long h[8];
+    CU(cudaMemcpyFromSymbol(h, g_s6_prof, sizeof(h)));
+    for (int i = 0; i < 8; ++i) out[i] = h[i];
+    if (reset) {
+        memset(h, 0, sizeof(h));
+        CU(cudaMemcpyToSymbol(g_s6_prof, h, sizeof(h)));
+    }
+#else
+    for (int i = 0; i < 8; ++i) out[i] = 0;
+    (void)reset;
+#endif
+    return ACOSS_OK;
+}
+
 int acoss_last_stage_ms(acoss_ctx* c, float out[5]) {
     if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
     if (!c->have_stage_ms) return fail(ACOSS_ERR_STATE, "no acoss_serra09_pairs call yet");

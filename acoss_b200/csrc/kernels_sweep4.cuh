@@ -180,16 +180,36 @@ __device__ __noinline__ double s4_cell_exact(const double* __restrict__ fi, cons
 // them from shared memory (any CTA size).
 template <int NQ>
 struct S4Keys {
+    static constexpr bool kPacked = true;
     uint4 k[NQ];
+    unsigned nk[2 * NQ];  // minus the upper 16 bits (15 significant) of every key, two per word
     __device__ __forceinline__ void load(const uint4* __restrict__ row4, int lane, int) {
 #pragma unroll
-        for (int q = 0; q < NQ; ++q) k[q] = row4[lane + 32 * q];
+        for (int q = 0; q < NQ; ++q) {
+            k[q] = row4[lane + 32 * q];
+            nk[2 * q] = __vneg2(__byte_perm(k[q].x, k[q].y, 0x7632));
+            nk[2 * q + 1] = __vneg2(__byte_perm(k[q].z, k[q].w, 0x7632));
+        }
     }
     __device__ __forceinline__ uint4 get(int q) const { return k[q]; }
     __device__ __forceinline__ int nq() const { return NQ; }
+    // number of keys whose upper half is <= t15 (0 <= t15 <= 32766): one DPX op + one packed add per TWO keys
+    __device__ __forceinline__ int count15(int t15) const {
+        const unsigned tt = (unsigned)(t15 + 1) * 0x00010001u, one = 0x00010001u;
+        unsigned a0 = 0, a1 = 0;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            a0 = __vadd2(a0, __viaddmin_s16x2_relu(nk[2 * q], tt, one));
+            a1 = __vadd2(a1, __viaddmin_s16x2_relu(nk[2 * q + 1], tt, one));
+        }
+        const unsigned a = __vadd2(a0, a1);
+        return __reduce_add_sync(kFullMask, (int)((a & 0xffffu) + (a >> 16)));
+    }
 };
 template <>
 struct S4Keys<0> {
+    static constexpr bool kPacked = false;
+    __device__ __forceinline__ int count15(int) const { return 0; }
     const uint4* p;
     int n;
     __device__ __forceinline__ void load(const uint4* __restrict__ row4, int lane, int nq_) {
@@ -329,7 +349,16 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
     int gallop = 0;
     bool done = false;
     for (int iter = 0; iter < 96 && !done; ++iter) {
-        const int c = s4_count(keys, t, lane);
+        int c;
+        if (K::kPacked) {
+            // thresholds of the form x * 2^16 + 0xffff are counted on the packed upper halves (half the
+            // instructions); any threshold inside the bracket is as good as another for the search
+            const int tr = t | 0xffff;
+            if (tr < 0x7fff0000 && !(real_hi && tr >= hi)) t = tr;
+            c = ((t & 0xffff) == 0xffff && t < 0x7fff0000) ? keys.count15(t >> 16) : s4_count(keys, t, lane);
+        } else {
+            c = s4_count(keys, t, lane);
+        }
         if (haveA && c != cA) {
             const float sp = fabsf((float)(t - tA)) * __fdividef(1.0f, fabsf((float)(c - cA)));
             if (sp >= 1.0f) spacing = sp;
@@ -450,14 +479,17 @@ __device__ __forceinline__ int s4_estimate(const K& keys, int jrank, int lane) {
         b2 = s4_umin(b2, s4_umax(b1, v.w));
         b1 = s4_umin(b1, v.w);
     }
-    const unsigned m2 = s4_umin(s4_umax(a1, b1), s4_umin(a2, b2));
-    int rank = 0;
+    // lanes with fewer than two keys hold 0xffffffff: clamp so that differences of two values keep their sign
+    const unsigned m2 = s4_umin(s4_umin(s4_umax(a1, b1), s4_umin(a2, b2)), (unsigned)kKeyInf);
+    unsigned r0 = 0, r1 = 0;  // strict rank: equal values (improbable) share a rank and the estimate is skipped
 #pragma unroll
-    for (int l = 0; l < 32; ++l) {
-        const unsigned o = __shfl_sync(kFullMask, m2, l);
-        rank += (o < m2 || (o == m2 && l < lane)) ? 1 : 0;
+    for (int l = 0; l < 32; l += 2) {
+        r0 += (__shfl_sync(kFullMask, m2, l) - m2) >> 31;
+        r1 += (__shfl_sync(kFullMask, m2, l + 1) - m2) >> 31;
     }
-    const unsigned hit = __ballot_sync(kFullMask, rank == jrank);
+    (void)lane;
+    const unsigned hit = __ballot_sync(kFullMask, (int)(r0 + r1) == jrank);
+    if (hit == 0u) return kKeyInf;
     const unsigned g = __shfl_sync(kFullMask, m2, __ffs((int)hit) - 1);
     return (g >= (unsigned)kKeyInf) ? kKeyInf : (int)g;
 }

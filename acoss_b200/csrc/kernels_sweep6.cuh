@@ -24,6 +24,12 @@
 
 namespace acoss {
 
+// profiling aid (debug flag bit 26): cycles spent by warp 0's lane 0 ... every warp's lane 0 in
+// [0] stage 2, [1] selection, [2] stage 1, [3] waiting at the period barrier, [4] periods, [5] items
+#ifndef ACOSS_EMU
+__device__ unsigned long long g_s6_prof[8];
+#endif
+
 constexpr int kS6Rows = 16;         // rows per period
 constexpr int kS6MaxThreads = 640;  // column songs of up to 631 frames (102 registers per thread)
 constexpr int kS6Pad = 9;            // NT >= Lc + kS6Pad: zero columns that flush the window (m = 9)
@@ -281,8 +287,17 @@ __global__ void __launch_bounds__(NT, s6_min_blocks(NT)) k_sweep6(Sweep4Args A) 
             __syncthreads();
         }
 
+#ifndef ACOSS_EMU
+        const bool prof = (A.flags & (1u << 26)) != 0 && lane == 0;
+        long long tp0 = 0, tp1 = 0, tp2 = 0, tp3 = 0, tp4 = 0, pa0 = 0, pa1 = 0, pa2 = 0, pa3 = 0;
+        if (prof && tid == 0) atomicAdd(&g_s6_prof[5], 1ull);
+#define S6_TICK(v) if (prof) v = clock64()
+#else
+#define S6_TICK(v)
+#endif
         for (int p = 0; p <= nper; ++p) {
             const int a0 = p * kS6Rows;
+            S6_TICK(tp0);
             if (!DB) {
                 if (p < nper) stage1(p);
                 __syncthreads();  // the slab of period p is complete
@@ -343,6 +358,7 @@ __global__ void __launch_bounds__(NT, s6_min_blocks(NT)) k_sweep6(Sweep4Args A) 
                 if (cb >= NT) cb -= NT;
             }
 
+            S6_TICK(tp1);
             // ---- selection of period p - 1: one row per warp
             if (p >= 1) {
                 const int ap = (p - 1) * kS6Rows;
@@ -386,9 +402,29 @@ __global__ void __launch_bounds__(NT, s6_min_blocks(NT)) k_sweep6(Sweep4Args A) 
                     spar ^= 1;
                 }
             }
+            S6_TICK(tp2);
             if (DB && p + 1 < nper) stage1(p + 1);  // overlaps the other warps' selection
+            S6_TICK(tp3);
             __syncthreads();  // the keys of period p and (DB) the slab of period p + 1 are complete
+#ifndef ACOSS_EMU
+            if (prof) {
+                tp4 = clock64();
+                pa0 += tp1 - tp0;
+                pa1 += tp2 - tp1;
+                pa2 += tp3 - tp2;
+                pa3 += tp4 - tp3;
+            }
+#endif
         }
+#ifndef ACOSS_EMU
+        if (prof) {
+            atomicAdd(&g_s6_prof[0], (unsigned long long)pa0);
+            atomicAdd(&g_s6_prof[1], (unsigned long long)pa1);
+            atomicAdd(&g_s6_prof[2], (unsigned long long)pa2);
+            atomicAdd(&g_s6_prof[3], (unsigned long long)pa3);
+            if (tid == 0) atomicAdd(&g_s6_prof[4], (unsigned long long)(nper + 1));
+        }
+#endif
     }
 }
 

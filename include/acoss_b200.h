@@ -158,6 +158,9 @@ int acoss_aggregate_songs(acoss_ctx* ctx, const void* full, int dtype, int layou
  * long-song sweeps on the main stream), "debug_flags" (profiling experiments). */
 int acoss_set_option(acoss_ctx* ctx, const char* name, int64_t value);
 
+/* Profiling aid (not part of the drop-in surface): cycle counters of the gen-6 sweep, see api.cu. */
+int acoss_debug_sweep6_cycles(acoss_ctx* ctx, uint64_t out[8], int reset);
+
 /* Counters for bench.py: kernels launched by this context since creation / last reset. */
 int64_t acoss_kernel_launches(acoss_ctx* ctx);
 void acoss_reset_counters(acoss_ctx* ctx);

@@ -362,6 +362,29 @@ inline unsigned __reduce_max_sync(unsigned, unsigned v) {
     emu::warp_barrier();
     return r;
 }
+// SIMD-in-word intrinsics used by the packed counting pass
+inline unsigned __byte_perm(unsigned x, unsigned y, unsigned sel) {
+    const uint64_t w = ((uint64_t)y << 32) | x;
+    unsigned r = 0;
+    for (int i = 0; i < 4; ++i) r |= (unsigned)((w >> (8 * ((sel >> (4 * i)) & 7))) & 0xff) << (8 * i);
+    return r;
+}
+inline unsigned __vneg2(unsigned a) {
+    const unsigned lo = (unsigned)(-(int)(int16_t)(a & 0xffff)) & 0xffffu, hi = (unsigned)(-(int)(int16_t)(a >> 16)) & 0xffffu;
+    return (hi << 16) | lo;
+}
+inline unsigned __vadd2(unsigned a, unsigned b) { return (((a >> 16) + (b >> 16)) << 16) | ((a + b) & 0xffffu); }
+inline unsigned __viaddmin_s16x2_relu(unsigned a, unsigned b, unsigned c) {
+    unsigned r = 0;
+    for (int h = 0; h < 2; ++h) {
+        int v = (int)(int16_t)((int16_t)(a >> (16 * h)) + (int16_t)(b >> (16 * h)));  // wraps like the hardware add
+        const int cc = (int16_t)(c >> (16 * h));
+        v = v < cc ? v : cc;
+        v = v > 0 ? v : 0;
+        r |= ((unsigned)v & 0xffffu) << (16 * h);
+    }
+    return r;
+}
 inline int __double2loint(double v) { return (int)(uint32_t)(emu::to_bits(v) & 0xffffffffu); }
 inline int __double2hiint(double v) { return (int)(uint32_t)(emu::to_bits(v) >> 32); }
 inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }
