@@ -55,6 +55,7 @@ SIGNATURES = {
     "acoss_kernel_launches": (ctypes.c_int64, [ctypes.c_void_p]),
     "acoss_reset_counters": (None, [ctypes.c_void_p]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
+    "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
 }
 
 

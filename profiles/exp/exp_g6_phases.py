@@ -10,8 +10,6 @@ n = len(songs)
 ctx = _native.Context(0); ctx.upload_songs(songs)
 ctx.set_option("sweep_gen", 6)
 f = ctx.lib.acoss_debug_sweep6_cycles
-f.restype = ctypes.c_int
-f.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]
 out = (ctypes.c_uint64 * 8)()
 for extra, name in ((0, "default"), (1 << 27, "estimator"), (1 << 30, "no selection")):
     ctx.set_option("debug_flags", (1 << 26) | extra)
