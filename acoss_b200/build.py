@@ -36,7 +36,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
             return OUT  # GPU box without a toolkit: use the prebuilt library that travelled
         raise RuntimeError("nvcc not found and no prebuilt %s" % OUT)
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "api.cu")]
+    defines = ["-D" + d for d in os.environ.get("ACOSS_NVCC_DEFINES", "").split(",") if d]  # e.g. ACOSS_S6_PROFILE
+    cmd = [nvcc] + NVCC_FLAGS + defines + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "api.cu")]
     subprocess.check_call(cmd)
     return OUT
 

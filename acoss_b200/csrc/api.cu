@@ -1273,10 +1273,11 @@ void acoss_reset_counters(acoss_ctx* c) {
 
 /* Profiling aid, not part of the drop-in surface: cycle counters of k_sweep6 (debug flag bit 26),
  * summed over every warp: [0] stage 2, [1] selection, [2] stage 1, [3] barrier wait, [4] periods (per CTA),
- * [5] items.  reset != 0 clears them. */
+ * [5] items.  reset != 0 clears them.  All zero unless the library was built with -DACOSS_S6_PROFILE
+ * (ACOSS_NVCC_DEFINES=ACOSS_S6_PROFILE python -m acoss_b200.build --force). */
 int acoss_debug_sweep6_cycles(acoss_ctx* c, uint64_t out[8], int reset) {
     if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
-#ifndef ACOSS_EMU
+#if ACOSS_S6_PROF
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     unsigned long long h[8];

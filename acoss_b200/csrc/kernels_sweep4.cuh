@@ -178,17 +178,25 @@ __device__ __noinline__ double s4_cell_exact(const double* __restrict__ fi, cons
 // The keys of one strip row as seen by one lane: quads lane, lane+32, ...  NQ > 0 keeps them in
 // registers for the whole selection (every pass is then pure integer ALU work); NQ == 0 streams
 // them from shared memory (any CTA size).
+// ACOSS_S4_PACKED_COUNT=1: counting passes on packed 15-bit keys (DPX).  Measured on the B200: half the
+// instructions per pass, no change in time (the selection is latency bound), and the 2 NQ extra
+// registers push the 128-register kernels into spills -- off by default.
+#ifndef ACOSS_S4_PACKED_COUNT
+#define ACOSS_S4_PACKED_COUNT 0
+#endif
 template <int NQ>
 struct S4Keys {
-    static constexpr bool kPacked = true;
+    static constexpr bool kPacked = ACOSS_S4_PACKED_COUNT != 0;
     uint4 k[NQ];
-    unsigned nk[2 * NQ];  // minus the upper 16 bits (15 significant) of every key, two per word
+    unsigned nk[kPacked ? 2 * NQ : 1];  // minus the upper 16 bits (15 significant) of every key, two per word
     __device__ __forceinline__ void load(const uint4* __restrict__ row4, int lane, int) {
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
             k[q] = row4[lane + 32 * q];
-            nk[2 * q] = __vneg2(__byte_perm(k[q].x, k[q].y, 0x7632));
-            nk[2 * q + 1] = __vneg2(__byte_perm(k[q].z, k[q].w, 0x7632));
+            if (kPacked) {
+                nk[kPacked ? 2 * q : 0] = __vneg2(__byte_perm(k[q].x, k[q].y, 0x7632));
+                nk[kPacked ? 2 * q + 1 : 0] = __vneg2(__byte_perm(k[q].z, k[q].w, 0x7632));
+            }
         }
     }
     __device__ __forceinline__ uint4 get(int q) const { return k[q]; }
@@ -199,8 +207,8 @@ struct S4Keys {
         unsigned a0 = 0, a1 = 0;
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
-            a0 = __vadd2(a0, __viaddmin_s16x2_relu(nk[2 * q], tt, one));
-            a1 = __vadd2(a1, __viaddmin_s16x2_relu(nk[2 * q + 1], tt, one));
+            a0 = __vadd2(a0, __viaddmin_s16x2_relu(nk[kPacked ? 2 * q : 0], tt, one));
+            a1 = __vadd2(a1, __viaddmin_s16x2_relu(nk[kPacked ? 2 * q + 1 : 0], tt, one));
         }
         const unsigned a = __vadd2(a0, a1);
         return __reduce_add_sync(kFullMask, (int)((a & 0xffffu) + (a >> 16)));

@@ -24,10 +24,14 @@
 
 namespace acoss {
 
-// profiling aid (debug flag bit 26): cycles spent by warp 0's lane 0 ... every warp's lane 0 in
-// [0] stage 2, [1] selection, [2] stage 1, [3] waiting at the period barrier, [4] periods, [5] items
-#ifndef ACOSS_EMU
+// profiling aid (build with -DACOSS_S6_PROFILE, then debug flag bit 26): cycles spent by every warp's lane 0 in
+// [0] stage 2, [1] selection, [2] stage 1, [3] waiting at the period barrier, [4] periods, [5] items.
+// Compile-time because the 18 registers of the counters cost the 128-register kernels spills.
+#if defined(ACOSS_S6_PROFILE) && !defined(ACOSS_EMU)
+#define ACOSS_S6_PROF 1
 __device__ unsigned long long g_s6_prof[8];
+#else
+#define ACOSS_S6_PROF 0
 #endif
 
 constexpr int kS6Rows = 16;         // rows per period
@@ -287,7 +291,7 @@ __global__ void __launch_bounds__(NT, s6_min_blocks(NT)) k_sweep6(Sweep4Args A) 
             __syncthreads();
         }
 
-#ifndef ACOSS_EMU
+#if ACOSS_S6_PROF
         const bool prof = (A.flags & (1u << 26)) != 0 && lane == 0;
         long long tp0 = 0, tp1 = 0, tp2 = 0, tp3 = 0, tp4 = 0, pa0 = 0, pa1 = 0, pa2 = 0, pa3 = 0;
         if (prof && tid == 0) atomicAdd(&g_s6_prof[5], 1ull);
@@ -406,7 +410,7 @@ __global__ void __launch_bounds__(NT, s6_min_blocks(NT)) k_sweep6(Sweep4Args A) 
             if (DB && p + 1 < nper) stage1(p + 1);  // overlaps the other warps' selection
             S6_TICK(tp3);
             __syncthreads();  // the keys of period p and (DB) the slab of period p + 1 are complete
-#ifndef ACOSS_EMU
+#if ACOSS_S6_PROF
             if (prof) {
                 tp4 = clock64();
                 pa0 += tp1 - tp0;
@@ -416,7 +420,7 @@ __global__ void __launch_bounds__(NT, s6_min_blocks(NT)) k_sweep6(Sweep4Args A) 
             }
 #endif
         }
-#ifndef ACOSS_EMU
+#if ACOSS_S6_PROF
         if (prof) {
             atomicAdd(&g_s6_prof[0], (unsigned long long)pa0);
             atomicAdd(&g_s6_prof[1], (unsigned long long)pa1);
