@@ -21,6 +21,7 @@ FLAG_DMAX_CLEAN = 1 << 1
 FLAG_NO_SWAP = 1 << 2
 FLAG_NON_MUTUAL = 1 << 3
 FLAG_WANT_SW = 1 << 4
+FLAG_DEVICE_INPUT = 1 << 8
 
 _c_i32p = ctypes.POINTER(ctypes.c_int32)
 _c_i64p = ctypes.POINTER(ctypes.c_int64)
@@ -45,6 +46,9 @@ SIGNATURES = {
     "acoss_aggregate_songs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, _c_i64p, _c_i32p,
                                              ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, _c_i64p, ctypes.c_void_p]),
+    "acoss_eval_ranks": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, _c_i32p, _c_i32p, _c_i32p,
+                                        ctypes.c_int32, _c_i64p, _c_i32p, ctypes.c_uint32]),
+    "acoss_last_eval_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_dp_packed": (ctypes.c_int, [ctypes.c_void_p, _c_u32p, _c_i64p, _c_i32p, _c_i32p, ctypes.c_int32,
                                        ctypes.c_uint32, _c_f32p]),
     "acoss_qmax": (ctypes.c_int, [ctypes.c_void_p, _c_u8p, ctypes.c_int32, ctypes.c_int32, _c_f32p]),
@@ -290,6 +294,33 @@ class Context:
         res = [out[o * bins:(o + int(l)) * bins].reshape(int(l), bins).T for o, l in zip(ooffs, L)]
         return (res, g) if want_gchroma else res
 
+    def eval_ranks(self, D, cliques, device_ptr=None):
+        """The rank loop of CoverAlgorithm.getEvalStatistics (CoverAlgorithm.py:345-382) on the device.
+        D: (n, n) float32 score matrix (host), or None with device_ptr = address of such a matrix
+        in device memory (a torch tensor's data_ptr()) and n given by the cliques.  cliques: list
+        of lists of song indices, in the order of CoverAlgorithm.cliques.  Returns (iranks, Ks,
+        n_rows): iranks = list, one int32 array of K - 1 ascending ranks per song of every clique
+        with K >= 2 (clique-contiguous order, cliques by descending size), Ks = sorted sizes."""
+        order, Ks, cstart, csize, offs, rows, total = eval_layout(cliques)
+        n = int(order.size)
+        out = np.zeros(max(total, 1), np.int32)
+        if device_ptr is None:
+            D = np.ascontiguousarray(D, dtype=np.float32)
+            if D.shape != (n, n):
+                raise ValueError("D must be (%d, %d)" % (n, n))
+            ptr, flags = D.ctypes.data_as(ctypes.c_void_p), 0
+        else:
+            ptr, flags = ctypes.c_void_p(int(device_ptr)), FLAG_DEVICE_INPUT
+        rc = self.lib.acoss_eval_ranks(self._h, ptr, n, _ptr(order, _c_i32p), _ptr(cstart, _c_i32p),
+                                       _ptr(csize, _c_i32p), rows, _ptr(offs, _c_i64p), _ptr(out, _c_i32p), flags)
+        self._check(rc, "acoss_eval_ranks")
+        return [out[o:o + k - 1] for o, k in zip(offs[:rows], csize[:rows])], Ks, rows
+
+    def last_eval_ms(self):
+        out = np.zeros(1, np.float32)
+        self._check(self.lib.acoss_last_eval_ms(self._h, _ptr(out, _c_f32p)), "acoss_last_eval_ms")
+        return float(out[0])
+
     def dp_packed(self, plots, flags=0, want_sw=False):
         """plots: list of uint8 (rows, cols) binary matrices.  Returns (B, 3) [qmax, dmax, sw]."""
         B = len(plots)
@@ -350,6 +381,34 @@ class Context:
         out = np.zeros(5, np.float32)
         self._check(self.lib.acoss_last_stage_ms(self._h, _ptr(out, _c_f32p)), "acoss_last_stage_ms")
         return dict(zip(["oti", "thresholds", "crp", "dp", "total"], out.tolist()))
+
+
+def eval_layout(cliques):
+    """Host bookkeeping of getEvalStatistics step 1 (CoverAlgorithm.py:345-357): cliques sorted by
+    size (descending; np.argsort(-Ks) as the reference calls it), songs unrolled in that order.
+    Returns order (position -> song), Ks, and for the leading positions that belong to cliques of
+    >= 2 songs: clique start, clique size, output offsets; their count; total number of ranks."""
+    cl = [list(c) for c in cliques]
+    Ks = np.array([len(c) for c in cl], dtype=np.int64)
+    idx = np.argsort(-Ks)
+    Ks = Ks[idx]
+    order = np.array([s for i in idx for s in cl[i]], dtype=np.int32)
+    big = Ks >= 2
+    # the reference stops at the first clique with fewer than two songs (:374-377)
+    nbig = int(np.argmin(big)) if not big.all() else len(Ks)
+    Kb = Ks[:nbig]
+    starts = np.concatenate(([0], np.cumsum(Kb)))[:-1] if nbig else np.zeros(0, np.int64)
+    cstart = np.repeat(starts, Kb).astype(np.int32)
+    csize = np.repeat(Kb, Kb).astype(np.int32)
+    rows = int(cstart.size)
+    offs = np.zeros(max(rows, 1), np.int64)
+    if rows > 1:
+        offs[1:rows] = np.cumsum(csize[:-1].astype(np.int64) - 1)
+    total = int((csize.astype(np.int64) - 1).sum())
+    if rows == 0:
+        cstart = np.zeros(1, np.int32)
+        csize = np.zeros(1, np.int32)
+    return order, Ks, cstart, csize, offs, rows, total
 
 
 def pack_bits(B):

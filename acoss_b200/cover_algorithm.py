@@ -19,7 +19,7 @@ import warnings
 
 import numpy as np
 
-from . import hdf5io
+from . import _native, hdf5io
 
 
 class CoverAlgorithm(object):
@@ -277,42 +277,32 @@ class CoverAlgorithm(object):
                 print('Could not clean-up automatically.')
 
     # ------------------------------------------------------------------ evaluation
-    def getEvalStatistics(self, similarity_type, topsidx=[1, 10, 100, 1000]):
-        """MR, MRR, MDR, MAP and Top-K for one similarity measure, plus a CSV row
-        (CoverAlgorithm.py:330-418).  The reference's O(N^2) Python rank loop (:367-390) is
-        replaced by an equivalent vectorised rank computation."""
-        from itertools import chain
-        D = np.array(self.Ds[similarity_type], dtype=np.float32)
+    def eval_ranks(self, similarity_type):
+        """Step 1 + the sort and rank loop of getEvalStatistics (CoverAlgorithm.py:345-382) on the
+        device (acoss_eval_ranks, csrc/kernels_eval.cuh): returns (ranks, AllMap) as the reference
+        builds them, NaN where the reference leaves NaN."""
+        D = np.ascontiguousarray(self.Ds[similarity_type], dtype=np.float32)
         N = D.shape[0]
+        if getattr(self, '_eval_ctx', None) is None:
+            self._eval_ctx = _native.Context(getattr(self, 'device', 0))
         cliques = [list(self.cliques[s]) for s in self.cliques]
-        Ks = np.array([len(c) for c in cliques])
-        idx = np.argsort(-Ks, kind="stable")
-        Ks = Ks[idx]
-        cliques = [cliques[i] for i in idx]
-        idx = np.array(list(chain(*cliques)), dtype=int)
-        D = D[idx, :]
-        D = D[:, idx]
-        np.fill_diagonal(D, -np.inf)
-        order = np.argsort(-D, 1)
+        iranks, Ks, rows = self._eval_ctx.eval_ranks(D, cliques)
         ranks = np.nan * np.ones(N)
         AllMap = np.nan * np.ones(N)
-        starts = np.concatenate(([0], np.cumsum(Ks)[:-1]))
-        for c, (startidx, K) in enumerate(zip(starts, Ks)):
-            if K < 2:
-                break  # cliques are sorted by size: the rest are singletons (CoverAlgorithm.py:374-377)
-            stop = False
-            for i in range(startidx, startidx + K):
-                inclique = (order[i] >= startidx) & (order[i] < startidx + K)
-                iranks = (np.nonzero(inclique)[0] + 1)[0:-1]  # the song itself comes last (-inf)
-                if len(iranks) == 0:
-                    warnings.warn("Recalling 0 songs for clique of size %i at song index %i" % (K, i))
-                    stop = True
-                    break
-                ranks[i] = iranks[0]
-                P = np.arange(1, K, dtype=np.float64) / iranks.astype(np.float64)
-                AllMap[i] = np.mean(P)
-            if stop:
-                break
+        for i in range(rows):
+            ir = iranks[i]
+            ranks[i] = ir[0]
+            # P = [j / r for j, r in zip(range(1, K), iranks)]; np.mean(P)   (CoverAlgorithm.py:387-389)
+            AllMap[i] = np.mean(np.arange(1, ir.size + 1, dtype=np.float64) / ir.astype(np.float64))
+        return ranks, AllMap
+
+    def getEvalStatistics(self, similarity_type, topsidx=[1, 10, 100, 1000]):
+        """MR, MRR, MDR, MAP and Top-K for one similarity measure, plus a CSV row
+        (CoverAlgorithm.py:330-418).  The argsort of the N x N matrix and the O(N^2) Python rank
+        loop (:362-382) run on the device; the float64 statistics follow here from the integer
+        ranks exactly as the reference computes them."""
+        N = self.Ds[similarity_type].shape[0]
+        ranks, AllMap = self.eval_ranks(similarity_type)
         MAP = np.nanmean(AllMap)
         ranks = ranks[np.isnan(ranks) == 0]
         MR = np.mean(ranks)

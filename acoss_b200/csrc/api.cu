@@ -24,6 +24,7 @@
 #include "kernels_sweep5.cuh"
 #include "kernels_sweep6.cuh"
 #include "kernels_feat.cuh"
+#include "kernels_eval.cuh"
 
 #ifdef ACOSS_EMU
 #define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
@@ -152,6 +153,8 @@ struct acoss_ctx {
     int64_t launches = 0;
     float stage_ms[5] = {0, 0, 0, 0, 0};
     bool have_stage_ms = false;
+    float eval_ms = -1.f;  // device time of the last k_eval_ranks launch
+    DevBuf eval_D;         // score matrix of acoss_eval_ranks when it arrives from the host
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
@@ -795,7 +798,7 @@ int acoss_destroy(acoss_ctx* c) {
     DevBuf* bufs[] = {&c->frames, &c->norms, &c->offs, &c->gchroma, &c->pairs, &c->items, &c->counters,
                       &c->seps, &c->crp, &c->bnd, &c->qout, &c->dout, &c->swout, &c->otiout, &c->gscratch,
                       &c->dense_in, &c->dense_desc, &c->dense_starts,
-                      &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb};
+                      &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb, &c->eval_D};
     for (DevBuf* b : bufs) b->release();
     c->h_stage.release();
     for (int i = 0; i < 5; ++i)
@@ -1235,6 +1238,85 @@ int acoss_aggregate_songs(acoss_ctx* c, const void* full, int dtype, int layout,
         CU(cudaStreamSynchronize(c->stream));
         s0 = s1;
     }
+    return ACOSS_OK;
+}
+
+/* F2 row: the rank computation of CoverAlgorithm.getEvalStatistics (CoverAlgorithm.py:345-382). */
+int acoss_eval_ranks(acoss_ctx* c, const float* D, int64_t n, const int32_t* order, const int32_t* clique_start,
+                     const int32_t* clique_size, int32_t rows, const int64_t* out_offsets, int32_t* iranks_out,
+                     uint32_t flags) {
+    if (!c) return fail(ACOSS_ERR_ARG, "context is null");
+    if (n < 0 || rows < 0 || rows > n) return fail(ACOSS_ERR_ARG, "bad sizes (n %lld, rows %d)", (long long)n, rows);
+    if (rows == 0) return ACOSS_OK;
+    if (!D || !order || !clique_start || !clique_size || !out_offsets || !iranks_out)
+        return fail(ACOSS_ERR_ARG, "null argument");
+    if (n > 0x7fffffffLL) return fail(ACOSS_ERR_ARG, "n too large");
+    // validate the clique description: order is a permutation, every active row lies inside its clique
+    std::vector<int32_t> pos((size_t)n, -1);
+    for (int64_t p = 0; p < n; ++p) {
+        const int32_t s = order[p];
+        if (s < 0 || s >= n || pos[(size_t)s] >= 0) return fail(ACOSS_ERR_ARG, "order is not a permutation of 0..n-1");
+        pos[(size_t)s] = (int32_t)p;
+    }
+    int64_t total = 0;
+    for (int p = 0; p < rows; ++p) {
+        const int32_t st = clique_start[p], K = clique_size[p];
+        if (K < 2 || st < 0 || (int64_t)st + K > n || p < st || p >= st + K)
+            return fail(ACOSS_ERR_ARG, "row %d: clique [%d, %d) does not hold it or has fewer than 2 songs", p, st, st + K);
+        if (out_offsets[p] != total) return fail(ACOSS_ERR_ARG, "out_offsets[%d] must be the running sum of (K - 1)", p);
+        total += K - 1;
+    }
+    CU(cudaSetDevice(c->device));
+    const float* d_D = D;
+    if (!(flags & ACOSS_FLAG_DEVICE_INPUT)) {
+        CU(c->eval_D.reserve((size_t)n * (size_t)n * sizeof(float)));
+        CU(cudaMemcpyAsync(c->eval_D.p, D, (size_t)n * (size_t)n * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+        d_D = c->eval_D.as<float>();
+    }
+    DevBuf meta, ranks;
+    struct Rel {
+        DevBuf *a, *b;
+        ~Rel() { a->release(); b->release(); }
+    } rel{&meta, &ranks};
+    const size_t meta_bytes = (size_t)n * 8 + (size_t)rows * 16 + 64;
+    CU(meta.reserve(meta_bytes));
+    CU(ranks.reserve((size_t)total * 8 + 64));
+    int32_t* d_order = meta.as<int32_t>();
+    int32_t* d_pos = d_order + n;
+    int32_t* d_cs = d_pos + n;
+    int32_t* d_ck = d_cs + rows;
+    int64_t* d_off = reinterpret_cast<int64_t*>(meta.as<char>() + (((size_t)n * 8 + (size_t)rows * 8 + 15) & ~(size_t)15));
+    CU(cudaMemcpyAsync(d_order, order, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_pos, pos.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_cs, clique_start, (size_t)rows * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_ck, clique_size, (size_t)rows * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_off, out_offsets, (size_t)rows * 8, cudaMemcpyHostToDevice, c->stream));
+    EvalArgs A;
+    A.D = d_D;
+    A.order = d_order;
+    A.pos = d_pos;
+    A.cstart = d_cs;
+    A.csize = d_ck;
+    A.out_off = d_off;
+    A.raw = ranks.as<int32_t>();
+    A.out = A.raw + total;
+    A.n = n;
+    A.rows = rows;
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    ACOSS_LAUNCH(k_eval_ranks, rows, kEvalThreads, 0, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    CU(cudaMemcpyAsync(iranks_out, A.out, (size_t)total * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaEventElapsedTime(&c->eval_ms, c->ev[0], c->ev[1]));
+    return ACOSS_OK;
+}
+
+int acoss_last_eval_ms(acoss_ctx* c, float* out) {
+    if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
+    if (c->eval_ms < 0.f) return fail(ACOSS_ERR_STATE, "no acoss_eval_ranks call yet");
+    *out = c->eval_ms;
     return ACOSS_OK;
 }
 

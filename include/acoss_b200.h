@@ -26,6 +26,10 @@
  *                           same argument order and return value; the caller's float D
  *                           table is not needed (and not filled)
  *   acoss_dp_packed         batched qmax/dmax/sw over caller-supplied bit-packed CRPs
+ *   acoss_aggregate_songs   Serra09.load_features' block aggregation + global_chroma
+ *                           (benchmarking/Serra09.py:24-28, 96-114)
+ *   acoss_eval_ranks        the sort + rank loop of CoverAlgorithm.getEvalStatistics
+ *                           (benchmarking/CoverAlgorithm.py:345-382)
  */
 #ifndef ACOSS_B200_H
 #define ACOSS_B200_H
@@ -58,6 +62,8 @@ typedef struct acoss_ctx acoss_ctx;
                                              is put on the columns (the DPs are transpose-invariant) */
 #define ACOSS_FLAG_NON_MUTUAL   (1u << 3) /* csm_to_binary instead of csm_to_binary_mutual (row kNN only) */
 #define ACOSS_FLAG_WANT_SW      (1u << 4) /* also run the constrained Smith-Waterman DP */
+#define ACOSS_FLAG_DEVICE_INPUT (1u << 8) /* acoss_eval_ranks: D is a device pointer on the context's device
+                                             (e.g. a torch tensor's data_ptr()); everything else stays host */
 
 const char* acoss_last_error(void);
 int acoss_version(void);
@@ -147,6 +153,30 @@ int acoss_aggregate_songs(acoss_ctx* ctx, const void* full, int dtype, int layou
                           const int64_t* offsets, const int32_t* nframes, int32_t n_songs,
                           int32_t bins, int32_t fac, int32_t aggregate, int32_t zero_nonfinite,
                           void* out, const int64_t* out_offsets, void* gchroma_out);
+
+/*
+ * The step after the path (CoverAlgorithm.getEvalStatistics, benchmarking/CoverAlgorithm.py:330-418)
+ * on the device: for every song of a clique with at least two members, the 1-based positions of
+ * the clique's OTHER songs in that song's row of the n x n score matrix D (float32, row-major, as
+ * CoverAlgorithm.Ds[type]; the diagonal is ignored) sorted by descending score -- the reference's
+ * `iranks[0:-1]` (:378-382).  Replaces np.argsort(-D, 1) (:362) and the O(n^2) Python loop
+ * (:367-382); equal scores keep the clique-contiguous order (a stable sort; the reference's
+ * introsort leaves it undefined).
+ *   order        [n]     the clique-contiguous song order `idx` of :355 (cliques sorted by size,
+ *                        descending), a permutation of 0..n-1
+ *   rows                 number of leading positions that belong to cliques of >= 2 songs
+ *   clique_start [rows]  position of the first song of the clique position p belongs to
+ *   clique_size  [rows]  K of that clique
+ *   out_offsets  [rows]  running sum of (K - 1): where row p's K - 1 ranks go in iranks_out
+ *   iranks_out           ascending ranks, sum of (K - 1) int32
+ * D is a host pointer, or a device pointer with ACOSS_FLAG_DEVICE_INPUT; the rest are host pointers.
+ * MR / MRR / MDR / MAP / Top-K follow on the host from the integer ranks (float64, numpy's order).
+ */
+int acoss_eval_ranks(acoss_ctx* ctx, const float* D, int64_t n, const int32_t* order,
+                     const int32_t* clique_start, const int32_t* clique_size, int32_t rows,
+                     const int64_t* out_offsets, int32_t* iranks_out, uint32_t flags);
+/* Device time (ms) of the k_eval_ranks launch of the last acoss_eval_ranks call. */
+int acoss_last_eval_ms(acoss_ctx* ctx, float* out);
 
 /* Test / tuning knobs (results never depend on them): "force_wide_sweep" (0/1),
  * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "chunk_pairs" (pairs per internal chunk),
