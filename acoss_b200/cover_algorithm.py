@@ -162,6 +162,13 @@ class CoverAlgorithm(object):
             if d and not os.path.exists(d):
                 os.makedirs(d)
             hdf5io.save(h5filename, {k: np.asarray(v) for k, v in self.Ds.items()})
+            # MATLAB twin of the same dict ('<prefix>_Ds.mat', one float32 N x N variable per similarity
+            # type): the reference's consumers under coverstats/ read .mat files, BASELINE names the layout
+            try:
+                from scipy.io import savemat
+                savemat("%s_Ds.mat" % self.get_cacheprefix(), {k: np.asarray(v) for k, v in self.Ds.items()})
+            except ImportError:  # scipy is optional on the host side
+                pass
         print("Elapsed Time All Pairwise: %.3g" % (time.time() - tic))
 
     # ------------------------------------------------------------------ batch mode

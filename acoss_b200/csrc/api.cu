@@ -1303,7 +1303,14 @@ int acoss_eval_ranks(acoss_ctx* c, const float* D, int64_t n, const int32_t* ord
     A.n = n;
     A.rows = rows;
     CU(cudaEventRecord(c->ev[0], c->stream));
-    ACOSS_LAUNCH(k_eval_ranks, rows, kEvalThreads, 0, c->stream, A);
+    int kmax = 0;
+    for (int p = 0; p < rows; ++p) kmax = std::max(kmax, (int)clique_size[p] - 1);
+    if (kmax <= 1) { ACOSS_LAUNCH(k_eval_ranks<1>, rows, kEvalThreads, 0, c->stream, A); }
+    else if (kmax <= 2) { ACOSS_LAUNCH(k_eval_ranks<2>, rows, kEvalThreads, 0, c->stream, A); }
+    else if (kmax <= 4) { ACOSS_LAUNCH(k_eval_ranks<4>, rows, kEvalThreads, 0, c->stream, A); }
+    else if (kmax <= 8) { ACOSS_LAUNCH(k_eval_ranks<8>, rows, kEvalThreads, 0, c->stream, A); }
+    else if (kmax <= 12) { ACOSS_LAUNCH(k_eval_ranks<12>, rows, kEvalThreads, 0, c->stream, A); }
+    else { ACOSS_LAUNCH(k_eval_ranks<kEvalMembers>, rows, kEvalThreads, 0, c->stream, A); }
     c->launches++;
     CU(cudaGetLastError());
     CU(cudaEventRecord(c->ev[1], c->stream));

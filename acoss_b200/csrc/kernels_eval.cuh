@@ -17,7 +17,7 @@
 namespace acoss {
 
 constexpr int kEvalThreads = 256;
-constexpr int kEvalMembers = 16;  // clique members counted per pass over the row
+constexpr int kEvalMembers = 16;  // most clique members counted per pass over the row (k_eval_ranks<NM>: NM <= 16)
 
 struct EvalArgs {
     const float* D;            // [n][n] row-major scores, as CoverAlgorithm.Ds[type] (symmetrised, diagonal ignored)
@@ -33,11 +33,15 @@ struct EvalArgs {
 };
 
 // One CTA per position p < rows (cliques are sorted by size, so the rows of cliques with K >= 2
-// are the first `rows` positions).
+// are the first `rows` positions).  NM = members counted per pass: the launch picks the smallest
+// instantiation that covers the largest clique (NM = 1 for sets of pairs such as covers80, 12 for
+// the benchmark subset's cliques of 13), because the inner loop costs 3 instructions per member
+// and element and decides whether the kernel is HBM- or issue-bound.
+template <int NM>
 __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks(EvalArgs A) {
-    __shared__ float s_val[kEvalMembers];
-    __shared__ int s_pos[kEvalMembers];
-    __shared__ int s_cnt[kEvalMembers];
+    __shared__ float s_val[NM];
+    __shared__ int s_pos[NM];
+    __shared__ int s_cnt[NM];
     const int p = (int)blockIdx.x;
     if (p >= A.rows) return;
     const int tid = (int)threadIdx.x, lane = tid & 31;
@@ -48,10 +52,10 @@ __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks(EvalArgs A) {
     int32_t* raw = A.raw + A.out_off[p];
     int32_t* out = A.out + A.out_off[p];
     const int nm_all = K - 1;  // members other than the row's own song
-    for (int m0 = 0; m0 < nm_all; m0 += kEvalMembers) {
-        const int nm = imin(kEvalMembers, nm_all - m0);
+    for (int m0 = 0; m0 < nm_all; m0 += NM) {
+        const int nm = imin(NM, nm_all - m0);
         __syncthreads();
-        if (tid < kEvalMembers) {
+        if (tid < NM) {
             float v = INFINITY;  // unused slots: nothing is greater than +inf
             int q = -1;
             if (tid < nm) {
@@ -64,11 +68,11 @@ __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks(EvalArgs A) {
             s_cnt[tid] = 0;
         }
         __syncthreads();
-        float mv[kEvalMembers];
-        int cnt[kEvalMembers];
+        float mv[NM];
+        int cnt[NM];
         float mmin = INFINITY;
 #pragma unroll
-        for (int t = 0; t < kEvalMembers; ++t) {
+        for (int t = 0; t < NM; ++t) {
             mv[t] = s_val[t];
             cnt[t] = 0;
             mmin = fminf(mmin, mv[t]);
@@ -87,7 +91,7 @@ __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks(EvalArgs A) {
             for (int u = 0; u < 4; ++u) {
                 bool eq = false;
 #pragma unroll
-                for (int t = 0; t < kEvalMembers; ++t) {
+                for (int t = 0; t < NM; ++t) {
                     cnt[t] += (v[u] > mv[t]) ? 1 : 0;
                     eq = eq || (v[u] == mv[t]);
                 }
@@ -97,14 +101,14 @@ __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks(EvalArgs A) {
                     if (j < n && j != i) {
                         const int pj = A.pos[j];
 #pragma unroll
-                        for (int t = 0; t < kEvalMembers; ++t)
+                        for (int t = 0; t < NM; ++t)
                             cnt[t] += (v[u] == mv[t] && pj < s_pos[t]) ? 1 : 0;
                     }
                 }
             }
         }
 #pragma unroll
-        for (int t = 0; t < kEvalMembers; ++t) {
+        for (int t = 0; t < NM; ++t) {
             const int s = warp_sum(cnt[t]);
             if (lane == 0 && s != 0) atomicAdd(&s_cnt[t], s);
         }

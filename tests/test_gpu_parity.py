@@ -57,6 +57,32 @@ def test_long_songs_vs_oracle(ctx):
     pc.check_against_oracle(ctx, songs, pairs[:2], m=20, kappa=0.095, flags=0)
 
 
+def test_stress_config_4096_frames(ctx):
+    """BASELINE configs[4]: 4096-frame songs, m = 20, kappa = 0.095 (M = N = 4077, k = 387).  One pair against the
+    oracle bit for bit (the oracle's Python diagonal loop takes seconds at this size); the rest of a mixed
+    1024..4096 batch against size-independent properties: (i, j) and (j, i) give transposed CRPs and equal
+    scores, and the batched call equals the one-pair calls (variable-length batching)."""
+    songs, _ = synth.make_song_set("covers80", seed=4096, n_songs=2, fixed_length=4096)
+    songs += synth.make_song_set("covers80", seed=4097, n_songs=4, length_range=(1024, 4096))[0]
+    n, tied = pc.check_against_oracle(ctx, songs, np.array([(0, 1)], np.int32), m=20, kappa=0.095,
+                                      flags=_native.FLAG_NO_SWAP)
+    assert n == 1 and tied == 0
+    pairs = np.array([(0, 1), (1, 0), (2, 3), (3, 2), (4, 5), (5, 4), (0, 4), (2, 1)], np.int32)
+    r = ctx.serra09_pairs(pairs, m=20, kappa=0.095, flags=_native.FLAG_NO_SWAP, want_crp=True)
+    assert tuple(r["shape"][0]) == (4077, 4077)
+    for a, b in ((0, 1), (2, 3), (4, 5)):
+        # OTI(i, j) and OTI(j, i) are complementary rotations, so the two plots are transposes of each other
+        assert (12 - r["oti"][a]) % 12 == r["oti"][b]
+        assert np.array_equal(r["crp"][a], r["crp"][b].T)
+        assert r["qmax_raw"][a] == r["qmax_raw"][b]
+    for p in (2, 6, 7):
+        one = ctx.serra09_pairs(pairs[p:p + 1], m=20, kappa=0.095, flags=_native.FLAG_NO_SWAP, want_crp=True)
+        assert np.array_equal(one["crp"][0], r["crp"][p])
+        assert one["qmax_raw"][0] == r["qmax_raw"][p] and one["dmax_raw"][0] == r["dmax_raw"][p]
+    dens = r["crp"][0].mean()
+    assert 0.02 < dens < 0.095
+
+
 def test_mfcc_path_no_oti(ctx):
     # Serra09.py:177-184: 13 bins, no OTI / roll
     rng = np.random.default_rng(13)

@@ -26,6 +26,9 @@ def test_all_pairwise_matches_oracle_and_writes_artefacts(tmp_path, monkeypatch)
     saved = hdf5io.load("cache/Serra09_t24_Ds.h5")
     assert np.array_equal(saved["chroma_qmax"], ref["chroma_qmax"])
     assert os.path.exists("cache/Serra09_t24_clique_info.txt")
+    from scipy.io import loadmat
+    mat = loadmat("cache/Serra09_t24_Ds.mat")
+    assert mat["chroma_qmax"].dtype == np.float32 and np.array_equal(mat["chroma_dmax"], ref["chroma_dmax"])
     MR, MRR, MDR, MAP, tops = alg.getEvalStatistics("chroma_qmax")
     assert 0 < MAP <= 1 and MR >= 1
     # covers are recognisable in the synthetic set: the mate of most songs ranks first
