@@ -18,6 +18,7 @@
 #include "kernels_dp.cuh"
 #include "kernels_prep.cuh"
 #include "kernels_sweep.cuh"
+#include "kernels_sweep1t.cuh"
 #include "kernels_sweep2.cuh"
 #include "kernels_sweep3.cuh"
 #include "kernels_sweep4.cuh"
@@ -130,6 +131,7 @@ struct acoss_ctx {
     // per-chunk scratch
     DevBuf pairs, items, counters, seps, crp, bnd, qout, dout, swout, otiout, gscratch;
     DevBuf dense_in, dense_desc, dense_starts;
+    DevBuf tmat;                                // tiled long-song sweep: float64 T matrices of the chunk
     DevBuf lens, wnorm, wnmax, sepk, sepx, nb;  // gen-4 sweep: windowed norms, integer separators, nibble CRPs
     int wnorm_m = -1;                           // window the wnorm buffer was computed for
     PinBuf h_stage;
@@ -148,6 +150,8 @@ struct acoss_ctx {
                                    // (kernels_sweep2.cuh); 3: warp-specialised variant of 2 (kernels_sweep3.cuh)
     int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
     int opt_single_stream = 0;     // 1: no side stream (profiling / debugging)
+    int opt_tiled_wide = 1;        // 1: column songs beyond the fast kernels go through the tiled sweep
+                                   // (kernels_sweep1t.cuh); 0: through the one-CTA general sweep (kernels_sweep.cuh)
     uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
     // accounting
     int64_t launches = 0;
@@ -163,6 +167,7 @@ namespace {
 constexpr int64_t kMaxChunkSepDoubles = (int64_t)1 << 28;  // 2 GiB
 constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
 constexpr int64_t kMaxChunkNbBytes = (int64_t)6 << 30;     // 6 GiB of nibble-byte CRPs (gen 4)
+constexpr int64_t kMaxWaveTmatDoubles = (int64_t)4 << 30;  // 32 GiB of T matrices per wave of the tiled long-song sweep
 constexpr int kCounterSlots = 96;
 constexpr int kG6Buckets = kS6Buckets;  // gen-6 launch buckets: CTAs of 128, 256, 512, 640 threads
 constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) threads, up to 128 * (b + 1) columns
@@ -170,6 +175,11 @@ constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) 
 struct ItemLists {
     std::vector<uint32_t> fast0[kFastBuckets], fast2[kFastBuckets];  // fast sweep: separators / separators + CRP
     std::vector<uint32_t> wide0, wide1;                              // general sweep (long songs): MODE 0 / MODE 1
+    std::vector<uint32_t> t3, tsel, t1;                              // tiled long-song sweep: T tiles, row selection, CRP tiles
+    int tsel_rows = 0, tsel_cols = 0;                                // largest Mo / No among tsel
+    // The T matrices are scratch between a tile sweep and its row selection only, so the chunk's tiled items run
+    // in WAVES that reuse one buffer (the DP still sees the whole chunk: one warp per pair needs many pairs).
+    std::vector<size_t> wave_t3, wave_tsel;                          // first item of every wave in t3 / tsel
     std::vector<uint32_t> g4_0[kFastBuckets], g4_2[kFastBuckets];    // gen-4 sweep: separators / CRP
     std::vector<uint32_t> g6_0[kS6Buckets], g6_2[kS6Buckets];  // gen-6 (DMMA) sweep by CTA size
     std::vector<uint32_t> g5_0[2], g5_2[2];                          // gen-5 sweep, 4 / 8 compute warps
@@ -340,6 +350,64 @@ int launch_sweep(acoss_ctx* c, const uint32_t* d_items, int n_items, int Wmax, i
     return ACOSS_OK;
 }
 
+template <int BINS, int MODE>
+int launch_sweep_tile(acoss_ctx* c, const uint32_t* d_items, int n_items, int m, unsigned int* d_counter, uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    auto kfn = k_sweep_tile<BINS, MODE>;
+    const size_t smem = tile_smem_bytes(m, BINS);
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, kTileThreads, smem));
+    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep_tile cannot be resident (smem %zu B)", smem);
+    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
+    TileArgs A;
+    memset(&A, 0, sizeof(A));
+    A.frames = c->frames.as<double>();
+    A.norms = c->norms.as<double>();
+    A.offs = c->offs.as<int64_t>();
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.counter = d_counter;
+    A.seps = c->seps.as<double>();
+    A.crp = c->crp.as<uint32_t>();
+    A.tmat = c->tmat.as<double>();
+    A.m = m;
+    A.flags = flags;
+    ACOSS_LAUNCH(kfn, grid, kTileThreads, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
+int launch_select_rows(acoss_ctx* c, const uint32_t* d_items, int n_items, int max_rows, int max_cols, int m) {
+    if (n_items <= 0) return ACOSS_OK;
+    SelArgs A;
+    memset(&A, 0, sizeof(A));
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    A.row_blocks = (max_rows + kSelWarps * kSelRowsPerWarp - 1) / (kSelWarps * kSelRowsPerWarp);
+    A.tmat = c->tmat.as<double>();
+    A.seps = c->seps.as<double>();
+    A.m = m;
+    // rows are staged in shared memory when four of them fit (otherwise the passes read global memory)
+    size_t smem = (size_t)kSelWarps * (size_t)max_cols * sizeof(double);
+    A.stage_cols = max_cols;
+    if (smem > (size_t)c->max_smem - 1024) {
+        smem = 0;
+        A.stage_cols = 0;
+    }
+    auto kfn = k_select_rows;
+    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t grid = (int64_t)n_items * A.row_blocks;
+    if (grid > 0x7fffffffLL) return fail(ACOSS_ERR_ARG, "too many rows for one selection launch");
+    ACOSS_LAUNCH(kfn, (int)grid, 32 * kSelWarps, smem, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
 template <int MODE>
 int launch_sweep5(acoss_ctx* c, const uint32_t* d_items, int n_items, int nwg, int m, unsigned int* d_counter, uint32_t flags) {
     if (n_items <= 0) return ACOSS_OK;
@@ -473,7 +541,9 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     // ---- host: work records + item lists
     std::vector<PairWork> W((size_t)n);
     ItemLists L;
-    int64_t sep_total = 0, crp_total = 0, bnd_total = 0, nb_total = 0;
+    int64_t sep_total = 0, crp_total = 0, bnd_total = 0, nb_total = 0, tmat_total = 0, tmat_peak = 0;
+    const bool tiled_ok = c->opt_tiled_wide && !c->opt_force_gscratch && tile_stride(m) >= 32 &&
+                          tile_smem_bytes(m, BINS) <= (size_t)c->max_smem - 1024 && n < (1 << (kTileItemBits - 1));
     const bool gen4_ok = c->opt_sweep_gen >= 4 && BINS == 12 && !c->opt_force_wide && s4_own_lanes(m) >= 16 &&
                          (size_t)s4_layout(32 * kFastBuckets, m, BINS).total <= (size_t)c->max_smem - 1024;
     const bool noswap = (flags & kFlagNoSwap) != 0;
@@ -498,6 +568,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         w.nb_off = 0;
         w.nb_stride = 0;
         w.pad1 = 0;
+        w.tm_off[0] = w.tm_off[1] = -1;
         w.sep_off = sep_total;
         w.crp_off = crp_total;
         const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
@@ -546,26 +617,48 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
                 continue;
             }
             const bool fast_ok = !c->opt_force_wide && std::max((size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows), (size_t)ws_smem_bytes(32 * kFastBuckets, m)) <= (size_t)c->max_smem - 1024;
-            if (!(nonmutual && dpo == 0)) {  // column separators of the CRP
-                const int Lc = Lc_of(other);
-                if (fast_ok && Lc <= kFastMaxCols) {
-                    L.fast0[(Lc - 1) / 128].push_back((uint32_t)p * 2 + other);
+            // separators of orientation o through the general sweep: tiled (T matrix + row selection) or one CTA
+            auto push_wide0 = [&](int o) {
+                const int Lc = Lc_of(o);
+                const int Mo = o ? w.N : w.M, No = o ? w.M : w.N;
+                if (tiled_ok && (int64_t)Mo * No <= kMaxWaveTmatDoubles) {
+                    if (L.wave_t3.empty() || tmat_total + (int64_t)Mo * No > kMaxWaveTmatDoubles) {
+                        L.wave_t3.push_back(L.t3.size());
+                        L.wave_tsel.push_back(L.tsel.size());
+                        tmat_total = 0;
+                    }
+                    tmat_peak = std::max(tmat_peak, tmat_total + (int64_t)Mo * No);
+                    for (int t = 0; t < tile_count(Lc, m); ++t)
+                        L.t3.push_back(((uint32_t)t << kTileItemBits) | ((uint32_t)p * 2 + o));
+                    L.tsel.push_back((uint32_t)p * 2 + o);
+                    L.tsel_rows = std::max(L.tsel_rows, Mo);
+                    L.tsel_cols = std::max(L.tsel_cols, No);
+                    w.tm_off[o] = tmat_total;
+                    tmat_total += (int64_t)Mo * No;
                 } else {
-                    L.wide0.push_back((uint32_t)p * 2 + other);
+                    L.wide0.push_back((uint32_t)p * 2 + o);
                     L.wide0_w = std::max(L.wide0_w, (Lc + wB - 1) / wB * wB);
                 }
+            };
+            if (!(nonmutual && dpo == 0)) {  // column separators of the CRP
+                const int Lc = Lc_of(other);
+                if (fast_ok && Lc <= kFastMaxCols)
+                    L.fast0[(Lc - 1) / 128].push_back((uint32_t)p * 2 + other);
+                else
+                    push_wide0(other);
             }
             {
                 const int Lc = Lc_of(dpo);
                 if (fast_ok && Lc <= kFastMaxCols) {
                     L.fast2[(Lc - 1) / 128].push_back((uint32_t)p);
                 } else {
-                    if (!(nonmutual && dpo == 1)) {
-                        L.wide0.push_back((uint32_t)p * 2 + dpo);
-                        L.wide0_w = std::max(L.wide0_w, (Lc + wB - 1) / wB * wB);
+                    if (!(nonmutual && dpo == 1)) push_wide0(dpo);
+                    if (tiled_ok) {
+                        for (int t = 0; t < tile_count(Lc, m); ++t) L.t1.push_back(((uint32_t)t << kTileItemBits) | (uint32_t)p);
+                    } else {
+                        L.wide1.push_back((uint32_t)p);
+                        L.wide1_w = std::max(L.wide1_w, (Lc + wB - 1) / wB * wB);
                     }
-                    L.wide1.push_back((uint32_t)p);
-                    L.wide1_w = std::max(L.wide1_w, (Lc + wB - 1) / wB * wB);
                 }
             }
         }
@@ -586,7 +679,9 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         CU(c->sepx.reserve((size_t)std::max<int64_t>(sep_total, 1) * sizeof(double)));
         CU(c->nb.reserve((size_t)std::max<int64_t>(nb_total, 16)));
     }
-    size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size();
+    if (tmat_peak > 0) CU(c->tmat.reserve((size_t)tmat_peak * sizeof(double)));
+    size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size() +
+                     L.t3.size() + L.tsel.size() + L.t1.size();
     for (int b = 0; b < kFastBuckets; ++b)
         n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
     for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
@@ -609,6 +704,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     for (int b = 0; b < kFastBuckets; ++b) o_fast2[b] = put(L.fast2[b]);
     o_wide0 = put(L.wide0);
     o_wide1 = put(L.wide1);
+    const size_t o_t3 = put(L.t3), o_tsel = put(L.tsel), o_t1 = put(L.t1);
     o_dp4 = put(L.dp4);
     o_dp8 = put(L.dp8);
     o_dp16 = put(L.dp16);
@@ -659,7 +755,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     // each a long CTA.  Launched alone they leave most SMs idle (profiles/r01_g: 27 % of a step), so
     // they run on a second, higher-priority stream, first, and the persistent CTAs of the main sweeps
     // take the SMs that are left.  The two families never share a pair.
-    bool side_work = !L.wide0.empty() || !L.wide1.empty(), main_work = !L.g4_pack.empty();
+    bool side_work = !L.wide0.empty() || !L.wide1.empty() || !L.t3.empty() || !L.t1.empty(), main_work = !L.g4_pack.empty();
     for (int b = 0; b < kFastBuckets; ++b) side_work = side_work || !L.fast0[b].empty() || !L.fast2[b].empty();
     const bool side = side_work && main_work && !c->opt_single_stream;
     {
@@ -674,9 +770,17 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             c->stream = c->stream2;
         }
         // largest buckets first: their CTAs are the long ones
+        for (size_t wv = 0; wv < L.wave_t3.size(); ++wv) {
+            const size_t a3 = L.wave_t3[wv], b3 = wv + 1 < L.wave_t3.size() ? L.wave_t3[wv + 1] : L.t3.size();
+            const size_t as = L.wave_tsel[wv], bs = wv + 1 < L.wave_tsel.size() ? L.wave_tsel[wv + 1] : L.tsel.size();
+            if (wv > 0) CU(cudaMemsetAsync(d_cnt + 72, 0, sizeof(unsigned int), c->stream));  // the wave's work-queue head
+            if ((rc = launch_sweep_tile<BINS, 3>(c, d_items + o_t3 + a3, (int)(b3 - a3), m, d_cnt + 72, flags))) return rc;
+            if ((rc = launch_select_rows(c, d_items + o_tsel + as, (int)(bs - as), L.tsel_rows, L.tsel_cols, m))) return rc;
+        }
         if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)
             if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+        if ((rc = launch_sweep_tile<BINS, 1>(c, d_items + o_t1, (int)L.t1.size(), m, d_cnt + 73, flags))) return rc;
         if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)
             if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 2> : launch_sweep_ws<BINS, 2>)(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
@@ -798,7 +902,7 @@ int acoss_destroy(acoss_ctx* c) {
     DevBuf* bufs[] = {&c->frames, &c->norms, &c->offs, &c->gchroma, &c->pairs, &c->items, &c->counters,
                       &c->seps, &c->crp, &c->bnd, &c->qout, &c->dout, &c->swout, &c->otiout, &c->gscratch,
                       &c->dense_in, &c->dense_desc, &c->dense_starts,
-                      &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb, &c->eval_D};
+                      &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb, &c->eval_D, &c->tmat};
     for (DevBuf* b : bufs) b->release();
     c->h_stage.release();
     for (int i = 0; i < 5; ++i)
@@ -1334,6 +1438,8 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
         c->opt_force_wide = value != 0;
     else if (n == "force_gscratch")
         c->opt_force_gscratch = value != 0;
+    else if (n == "tiled_wide")
+        c->opt_tiled_wide = value != 0;
     else if (n == "sweep_gen") {
         if (value < 2 || value > 6) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2 .. 6");
         c->opt_sweep_gen = (int)value;

@@ -50,6 +50,7 @@ struct PairWork {
     int64_t nb_off;          // into the nibble-byte CRP arena of the gen-4 sweep (bytes)
     int32_t nb_stride;       // bytes per row there (= threads of the MODE 2 CTA)
     int32_t pad1;
+    int64_t tm_off[2];       // per orientation: the float64 T matrix of the tiled long-song sweep (doubles), -1 unused
 };
 
 // Named barriers (PTX bar.sync / bar.arrive with an explicit thread count): the producer /

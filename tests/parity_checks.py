@@ -127,14 +127,15 @@ def check_options_invariant(ctx, songs, pairs, m=9, kappa=0.095):
     """The tuning knobs select different kernels / scratch placements; results must not move."""
     ctx.upload_songs(songs)
     base = ctx.serra09_pairs(pairs, m=m, kappa=kappa, want_crp=True, want_sw=True, flags=_native.FLAG_NO_SWAP)
-    for opts in ({"force_wide_sweep": 1}, {"force_gscratch": 1}, {"dp_max_cpl": 16}, {"chunk_pairs": 3},
-                 {"force_wide_sweep": 1, "force_gscratch": 1, "dp_max_cpl": 8, "chunk_pairs": 2}):
+    for opts in ({"force_wide_sweep": 1}, {"force_wide_sweep": 1, "tiled_wide": 0}, {"force_gscratch": 1}, {"dp_max_cpl": 16},
+                 {"chunk_pairs": 3}, {"force_wide_sweep": 1, "force_gscratch": 1, "dp_max_cpl": 8, "chunk_pairs": 2}):
         for k, v in opts.items():
             ctx.set_option(k, v)
         try:
             r = ctx.serra09_pairs(pairs, m=m, kappa=kappa, want_crp=True, want_sw=True, flags=_native.FLAG_NO_SWAP)
         finally:
-            for k, v in {"force_wide_sweep": 0, "force_gscratch": 0, "dp_max_cpl": 4, "chunk_pairs": 1 << 18}.items():
+            for k, v in {"force_wide_sweep": 0, "force_gscratch": 0, "dp_max_cpl": 4, "chunk_pairs": 1 << 18,
+                         "tiled_wide": 1}.items():
                 ctx.set_option(k, v)
         for key in ("qmax_raw", "dmax_raw", "sw_raw", "oti"):
             assert np.array_equal(r[key], base[key]), "%s changed under %s" % (key, opts)

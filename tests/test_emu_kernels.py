@@ -42,6 +42,29 @@ def test_emu_options_invariant(ctx):
         assert base["qmax_raw"][p] == o["qmax_raw"] and base["dmax_raw"][p] == o["dmax_raw"]
 
 
+def test_emu_tiled_long_song_sweep(ctx):
+    """kernels_sweep1t.cuh under emulation: a column song that needs two tiles (1024 frame columns each, m - 1
+    overlap), T matrix + row selection + tiled CRP emission, against the oracle; then the one-CTA general sweep
+    (tiled_wide = 0) must give the same bits."""
+    songs, _ = synth.make_song_set("covers80", seed=51, n_songs=2, length_range=(40, 70))
+    songs += synth.make_song_set("covers80", seed=52, n_songs=1, fixed_length=1450)[0]
+    pairs = np.array([(0, 2), (2, 1)], np.int32)
+    n, tied = pc.check_against_oracle(ctx, songs, pairs, m=9, kappa=0.095, flags=_native.FLAG_NO_SWAP)
+    assert n == 2 and tied == 0
+    pc.check_against_oracle(ctx, songs, pairs[:1], m=20, kappa=0.095, flags=0)
+    ctx.set_option("force_wide_sweep", 1)
+    try:
+        a = ctx.serra09_pairs(pairs, m=9, kappa=0.095, want_crp=True)
+        ctx.set_option("tiled_wide", 0)
+        b = ctx.serra09_pairs(pairs, m=9, kappa=0.095, want_crp=True)
+    finally:
+        ctx.set_option("tiled_wide", 1)
+        ctx.set_option("force_wide_sweep", 0)
+    for x, y in zip(a["crp"], b["crp"]):
+        assert np.array_equal(x, y)
+    assert np.array_equal(a["qmax_raw"], b["qmax_raw"]) and np.array_equal(a["dmax_raw"], b["dmax_raw"])
+
+
 def test_emu_dense(ctx):
     assert pc.check_dense(ctx, [(20, 37), (45, 33), (5, 4)]) == 3
 
