@@ -391,7 +391,20 @@ int launch_select_rows(acoss_ctx* c, const uint32_t* d_items, int n_items, int m
     A.tmat = c->tmat.as<double>();
     A.seps = c->seps.as<double>();
     A.m = m;
-    // rows are staged in shared memory when four of them fit (otherwise the passes read global memory)
+    if (max_cols <= 32 * kSelThreads) {
+        // the row fits the registers of one CTA: CTA-per-row selection
+        A.row_blocks = (max_rows + kSelRowsPerCta - 1) / kSelRowsPerCta;
+        const int64_t grid = (int64_t)n_items * A.row_blocks;
+        if (grid > 0x7fffffffLL) return fail(ACOSS_ERR_ARG, "too many rows for one selection launch");
+        if (max_cols <= 4 * kSelThreads) { ACOSS_LAUNCH(k_select_rows_cta<4>, (int)grid, kSelThreads, 0, c->stream, A); }
+        else if (max_cols <= 16 * kSelThreads) { ACOSS_LAUNCH(k_select_rows_cta<16>, (int)grid, kSelThreads, 0, c->stream, A); }
+        else { ACOSS_LAUNCH(k_select_rows_cta<32>, (int)grid, kSelThreads, 0, c->stream, A); }
+        c->launches++;
+        CU(cudaGetLastError());
+        return ACOSS_OK;
+    }
+    // longer rows: one warp per row; rows are staged in shared memory when four of them fit (otherwise the passes
+    // read global memory)
     size_t smem = (size_t)kSelWarps * (size_t)max_cols * sizeof(double);
     A.stage_cols = max_cols;
     if (smem > (size_t)c->max_smem - 1024) {

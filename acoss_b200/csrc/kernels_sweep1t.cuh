@@ -271,4 +271,141 @@ __global__ void __launch_bounds__(32 * kSelWarps) k_select_rows(SelArgs A) {
     }
 }
 
+// CTA-per-row selection: the row's values live in the registers of 256 threads (EPT each), every counting pass
+// is register compares + one REDUX + one barrier.  Same separator as warp_select_sep: the midpoint between the
+// k-th and (k+1)-th smallest, exact float64 ties across the k-th position left out.
+constexpr int kSelThreads = 256;
+constexpr int kSelRowsPerCta = 32;
+
+__device__ __forceinline__ int cta_sum(int v, int* slots, int& par, int warp, int lane) {
+    v = warp_sum(v);
+    int* sl = slots + par * (kSelThreads / 32);
+    if (lane == 0) sl[warp] = v;
+    __syncthreads();
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < kSelThreads / 32; ++w) t += sl[w];
+    par ^= 1;  // the next reduction uses the other slot set: one barrier per reduction
+    return t;
+}
+__device__ __forceinline__ void cta_minmax(double& lo, double& hi, double* slots, int& par, int warp, int lane) {
+    lo = warp_min(lo);
+    hi = warp_max(hi);
+    double* sl = slots + par * 2 * (kSelThreads / 32);
+    if (lane == 0) {
+        sl[2 * warp] = lo;
+        sl[2 * warp + 1] = hi;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < kSelThreads / 32; ++w) {
+        lo = fmin(lo, sl[2 * w]);
+        hi = fmax(hi, sl[2 * w + 1]);
+    }
+    par ^= 1;
+}
+
+template <int EPT>
+__global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
+    __shared__ int s_cnt[2 * (kSelThreads / 32)];
+    __shared__ double s_mm[2 * 2 * (kSelThreads / 32)];
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int it = (int)(blockIdx.x / (unsigned)A.row_blocks), rb = (int)(blockIdx.x % (unsigned)A.row_blocks);
+    if (it >= A.n_items) return;
+    const uint32_t item = A.items[it];
+    const int pidx = (int)(item >> 1), orient = (int)(item & 1u);
+    const PairWork* pw = A.pairs + pidx;
+    const int Lr = orient ? pw->Lj : pw->Li, Lc = orient ? pw->Li : pw->Lj;
+    const int Mo = Lr - A.m + 1, No = Lc - A.m + 1;
+    if (Mo <= 0 || No <= 0) return;
+    const int k = orient ? pw->k_col : pw->k_row;
+    const int64_t rsep_off = pw->sep_off + (orient ? pw->M : 0);
+    const double* tm = A.tmat + pw->tm_off[orient];
+    int pc = 0, pm = 0;
+    double guess = __longlong_as_double(0x7ff8000000000000LL);  // NaN: no guess yet
+    const int i0 = rb * kSelRowsPerCta;
+    for (int i = i0; i < imin(i0 + kSelRowsPerCta, Mo); ++i) {
+        const double* row = tm + (int64_t)i * No;
+        double v[EPT];
+#pragma unroll
+        for (int e = 0; e < EPT; ++e) {
+            const int j = tid + e * kSelThreads;
+            v[e] = (j < No) ? row[j] : INF;  // +inf pads: never counted (thresholds are finite)
+        }
+        double sep;
+        if (k <= 0) {
+            sep = -INF;
+        } else if (k >= No) {
+            sep = INF;
+        } else {
+            double lo = INF, hi = -INF;
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) {
+                lo = fmin(lo, v[e]);
+                if (v[e] < INF) hi = fmax(hi, v[e]);
+            }
+            cta_minmax(lo, hi, s_mm, pm, warp, lane);
+            auto count_le = [&](double t) {
+                int c = 0;
+#pragma unroll
+                for (int e = 0; e < EPT; ++e) c += (v[e] <= t) ? 1 : 0;
+                return cta_sum(c, s_cnt, pc, warp, lane);
+            };
+            int clo = count_le(lo), chi = No;
+            double t = lo;
+            if (clo > k) {
+                sep = -INF;  // ties at the minimum straddle k
+            } else {
+                bool found = (clo == k);
+                if (!found) {
+                    const bool use_guess = (guess > lo) && (guess < hi);
+                    for (int iter = 0; iter < 400 && !found; ++iter) {
+                        if (iter == 0 && use_guess) {
+                            t = guess;
+                        } else {
+                            if (iter & 1)
+                                t = 0.5 * lo + 0.5 * hi;
+                            else
+                                t = lo + (hi - lo) * ((double)(k - clo) / (double)(chi - clo));
+                            if (!(t > lo && t < hi)) {
+                                t = 0.5 * lo + 0.5 * hi;
+                                if (!(t > lo && t < hi)) break;  // bracket collapsed: exact ties
+                            }
+                        }
+                        const int c = count_le(t);
+                        if (c == k) {
+                            found = true;
+                        } else if (c < k) {
+                            lo = t;
+                            clo = c;
+                        } else {
+                            hi = t;
+                            chi = c;
+                        }
+                    }
+                }
+                if (!found) t = lo;
+                double vk = INF, vk1 = INF;  // vk holds -max via min of negatives
+                double nvk = INF;
+#pragma unroll
+                for (int e = 0; e < EPT; ++e) {
+                    if (v[e] <= t)
+                        nvk = fmin(nvk, -v[e]);
+                    else
+                        vk1 = fmin(vk1, v[e]);
+                }
+                double a = nvk, b = -vk1;  // reduce min(nvk) and min(vk1) = -max(-vk1) in one call
+                cta_minmax(a, b, s_mm, pm, warp, lane);
+                vk = -a;
+                vk1 = -b;
+                sep = vk + 0.5 * (vk1 - vk);
+                if (!(sep < vk1)) sep = vk;
+            }
+        }
+        guess = sep;
+        if (tid == 0) A.seps[rsep_off + i] = sep;
+    }
+}
+
 }  // namespace acoss
