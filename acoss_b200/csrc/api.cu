@@ -179,7 +179,9 @@ struct ItemLists {
     int tsel_rows = 0, tsel_cols = 0;                                // largest Mo / No among tsel
     // The T matrices are scratch between a tile sweep and its row selection only, so the chunk's tiled items run
     // in WAVES that reuse one buffer (the DP still sees the whole chunk: one warp per pair needs many pairs).
-    std::vector<size_t> wave_t3, wave_tsel;                          // first item of every wave in t3 / tsel
+    std::vector<size_t> wave_t3, wave_tsel, wave_te;                 // first item of every wave in t3 / tsel / te
+    std::vector<uint32_t> te;                                        // pairs whose CRP comes from the stored T matrix
+    int te_rows = 0;
     std::vector<uint32_t> g4_0[kFastBuckets], g4_2[kFastBuckets];    // gen-4 sweep: separators / CRP
     std::vector<uint32_t> g6_0[kS6Buckets], g6_2[kS6Buckets];  // gen-6 (DMMA) sweep by CTA size
     std::vector<uint32_t> g5_0[2], g5_2[2];                          // gen-5 sweep, 4 / 8 compute warps
@@ -421,6 +423,28 @@ int launch_select_rows(acoss_ctx* c, const uint32_t* d_items, int n_items, int m
     return ACOSS_OK;
 }
 
+int launch_emit_crp(acoss_ctx* c, const uint32_t* d_items, int n_items, int max_rows, int m, uint32_t flags) {
+    if (n_items <= 0) return ACOSS_OK;
+    EmitArgs A;
+    memset(&A, 0, sizeof(A));
+    A.pairs = c->pairs.as<PairWork>();
+    A.items = d_items;
+    A.n_items = n_items;
+    const int rows_per_cta = (kEmitThreads / 32) * kEmitRowsPerWarp;
+    A.row_blocks = (max_rows + rows_per_cta - 1) / rows_per_cta;
+    A.tmat = c->tmat.as<double>();
+    A.seps = c->seps.as<double>();
+    A.crp = c->crp.as<uint32_t>();
+    A.m = m;
+    A.flags = flags;
+    const int64_t grid = (int64_t)n_items * A.row_blocks;
+    if (grid > 0x7fffffffLL) return fail(ACOSS_ERR_ARG, "too many rows for one emission launch");
+    ACOSS_LAUNCH(k_emit_crp, (int)grid, kEmitThreads, 0, c->stream, A);
+    c->launches++;
+    CU(cudaGetLastError());
+    return ACOSS_OK;
+}
+
 template <int MODE>
 int launch_sweep5(acoss_ctx* c, const uint32_t* d_items, int n_items, int nwg, int m, unsigned int* d_counter, uint32_t flags) {
     if (n_items <= 0) return ACOSS_OK;
@@ -638,6 +662,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
                     if (L.wave_t3.empty() || tmat_total + (int64_t)Mo * No > kMaxWaveTmatDoubles) {
                         L.wave_t3.push_back(L.t3.size());
                         L.wave_tsel.push_back(L.tsel.size());
+                        L.wave_te.push_back(L.te.size());
                         tmat_total = 0;
                     }
                     tmat_peak = std::max(tmat_peak, tmat_total + (int64_t)Mo * No);
@@ -653,12 +678,14 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
                     L.wide0_w = std::max(L.wide0_w, (Lc + wB - 1) / wB * wB);
                 }
             };
+            size_t wave_other = 0;  // wave of the other orientation's tiled item
             if (!(nonmutual && dpo == 0)) {  // column separators of the CRP
                 const int Lc = Lc_of(other);
                 if (fast_ok && Lc <= kFastMaxCols)
                     L.fast0[(Lc - 1) / 128].push_back((uint32_t)p * 2 + other);
                 else
                     push_wide0(other);
+                if (w.tm_off[other] >= 0) wave_other = L.wave_t3.size();
             }
             {
                 const int Lc = Lc_of(dpo);
@@ -666,7 +693,14 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
                     L.fast2[(Lc - 1) / 128].push_back((uint32_t)p);
                 } else {
                     if (!(nonmutual && dpo == 1)) push_wide0(dpo);
-                    if (tiled_ok) {
+                    // The CRP straight from the stored T matrix when its separators are complete inside the same
+                    // wave: the column separators come from a tiled item of this wave, or from a fast / one-CTA
+                    // sweep (those run before the waves); the row separators from the selection just pushed.
+                    const bool cols_ready = w.tm_off[other] < 0 || wave_other == L.wave_t3.size();
+                    if (tiled_ok && w.tm_off[dpo] >= 0 && cols_ready) {
+                        L.te.push_back((uint32_t)p);
+                        L.te_rows = std::max(L.te_rows, w.crp_rows);
+                    } else if (tiled_ok) {
                         for (int t = 0; t < tile_count(Lc, m); ++t) L.t1.push_back(((uint32_t)t << kTileItemBits) | (uint32_t)p);
                     } else {
                         L.wide1.push_back((uint32_t)p);
@@ -694,7 +728,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     }
     if (tmat_peak > 0) CU(c->tmat.reserve((size_t)tmat_peak * sizeof(double)));
     size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size() +
-                     L.t3.size() + L.tsel.size() + L.t1.size();
+                     L.t3.size() + L.tsel.size() + L.t1.size() + L.te.size();
     for (int b = 0; b < kFastBuckets; ++b)
         n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
     for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
@@ -717,7 +751,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     for (int b = 0; b < kFastBuckets; ++b) o_fast2[b] = put(L.fast2[b]);
     o_wide0 = put(L.wide0);
     o_wide1 = put(L.wide1);
-    const size_t o_t3 = put(L.t3), o_tsel = put(L.tsel), o_t1 = put(L.t1);
+    const size_t o_t3 = put(L.t3), o_tsel = put(L.tsel), o_t1 = put(L.t1), o_te = put(L.te);
     o_dp4 = put(L.dp4);
     o_dp8 = put(L.dp8);
     o_dp16 = put(L.dp16);
@@ -783,16 +817,18 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             c->stream = c->stream2;
         }
         // largest buckets first: their CTAs are the long ones
-        for (size_t wv = 0; wv < L.wave_t3.size(); ++wv) {
-            const size_t a3 = L.wave_t3[wv], b3 = wv + 1 < L.wave_t3.size() ? L.wave_t3[wv + 1] : L.t3.size();
-            const size_t as = L.wave_tsel[wv], bs = wv + 1 < L.wave_tsel.size() ? L.wave_tsel[wv + 1] : L.tsel.size();
-            if (wv > 0) CU(cudaMemsetAsync(d_cnt + 72, 0, sizeof(unsigned int), c->stream));  // the wave's work-queue head
-            if ((rc = launch_sweep_tile<BINS, 3>(c, d_items + o_t3 + a3, (int)(b3 - a3), m, d_cnt + 72, flags))) return rc;
-            if ((rc = launch_select_rows(c, d_items + o_tsel + as, (int)(bs - as), L.tsel_rows, L.tsel_cols, m))) return rc;
-        }
         if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)
             if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+        for (size_t wv = 0; wv < L.wave_t3.size(); ++wv) {
+            const size_t a3 = L.wave_t3[wv], b3 = wv + 1 < L.wave_t3.size() ? L.wave_t3[wv + 1] : L.t3.size();
+            const size_t as = L.wave_tsel[wv], bs = wv + 1 < L.wave_tsel.size() ? L.wave_tsel[wv + 1] : L.tsel.size();
+            const size_t ae = L.wave_te[wv], be = wv + 1 < L.wave_te.size() ? L.wave_te[wv + 1] : L.te.size();
+            if (wv > 0) CU(cudaMemsetAsync(d_cnt + 72, 0, sizeof(unsigned int), c->stream));  // the wave's work-queue head
+            if ((rc = launch_sweep_tile<BINS, 3>(c, d_items + o_t3 + a3, (int)(b3 - a3), m, d_cnt + 72, flags))) return rc;
+            if ((rc = launch_select_rows(c, d_items + o_tsel + as, (int)(bs - as), L.tsel_rows, L.tsel_cols, m))) return rc;
+            if ((rc = launch_emit_crp(c, d_items + o_te + ae, (int)(be - ae), L.te_rows, m, flags))) return rc;
+        }
         if ((rc = launch_sweep_tile<BINS, 1>(c, d_items + o_t1, (int)L.t1.size(), m, d_cnt + 73, flags))) return rc;
         if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)

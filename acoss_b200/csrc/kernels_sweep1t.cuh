@@ -51,6 +51,10 @@ struct TileArgs {
     uint32_t flags;
 };
 
+// ring layout: column c of a ring row sits at (c & 3) * 256 + (c >> 2), so that the four columns of a thread
+// are 256 doubles apart and a warp's accesses to one of them are contiguous (no bank conflicts)
+__device__ __forceinline__ int tile_ridx(int c) { return (c & 3) * kTileThreads + (c >> 2); }
+
 template <int BINS, int MODE>
 __global__ void __launch_bounds__(kTileThreads) k_sweep_tile(TileArgs A) {
     constexpr int CPL = kSweepCPL, THREADS = kTileThreads, W = kTileCols;
@@ -133,8 +137,9 @@ __global__ void __launch_bounds__(kTileThreads) k_sweep_tile(TileArgs A) {
             if (MODE == 1 && own[r]) cs[r] = (nonmutual && !orient) ? INF : A.seps[csep_off + c_lo + jl];
         }
 
+        int slot = 0;  // a % RD, kept by increment (RD is a runtime value: no integer division in the row loop)
         for (int a = 0; a < Lr; ++a) {
-            if ((a % kStageRows) == 0) {
+            if ((a & (kStageRows - 1)) == 0) {
                 for (int idx = tid; idx < kStageRows * XS; idx += THREADS) {
                     const int rr = idx / XS, k = idx - rr * XS;
                     const int a2 = a + rr;
@@ -152,7 +157,7 @@ __global__ void __launch_bounds__(kTileThreads) k_sweep_tile(TileArgs A) {
                 }
                 __syncthreads();
             }
-            const double* xr = xs + (a % kStageRows) * XS;
+            const double* xr = xs + (a & (kStageRows - 1)) * XS;
             double x[BINS];
 #pragma unroll
             for (int k = 0; k < BINS; ++k) x[k] = xr[k];
@@ -162,9 +167,11 @@ __global__ void __launch_bounds__(kTileThreads) k_sweep_tile(TileArgs A) {
             double rs = -INF;
             if (MODE == 1 && i >= 0) rs = (nonmutual && orient) ? INF : A.seps[rsep_off + i];
 
-            const double* ring1 = ring + (size_t)((a + RD - 1) % RD) * W;  // row a-1
-            const double* ringm = ring + (size_t)((a + 1) % RD) * W;       // row a-m
-            double* ring0 = ring + (size_t)(a % RD) * W;
+            const int slot1 = slot == 0 ? RD - 1 : slot - 1, slotm = slot + 1 == RD ? 0 : slot + 1;
+            const double* ring1 = ring + (size_t)slot1 * W;  // row a-1
+            const double* ringm = ring + (size_t)slotm * W;  // row a-m
+            double* ring0 = ring + (size_t)slot * W;
+            slot = slotm;
 
             double P[CPL], T[CPL];
 #pragma unroll
@@ -176,16 +183,16 @@ __global__ void __launch_bounds__(kTileThreads) k_sweep_tile(TileArgs A) {
                 const int lb = lb0 + r;
                 double pd;
                 if (r == 0)
-                    pd = (a > 0 && lb > 0) ? ring1[lb - 1] : 0.0;
+                    pd = (a > 0 && lb > 0) ? ring1[tile_ridx(lb - 1)] : 0.0;
                 else
                     pd = Pprev[r - 1];
                 P[r] = pd + C;
-                const double po = (a >= m && lb >= m) ? ringm[lb - m] : 0.0;
+                const double po = (a >= m && lb >= m) ? ringm[tile_ridx(lb - m)] : 0.0;
                 T[r] = P[r] - po;
             }
 #pragma unroll
             for (int r = 0; r < CPL; ++r) {
-                ring0[lb0 + r] = P[r];
+                ring0[r * kTileThreads + tid] = P[r];
                 Pprev[r] = P[r];
             }
             if (MODE == 3) {
@@ -323,7 +330,8 @@ __global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
     const int64_t rsep_off = pw->sep_off + (orient ? pw->M : 0);
     const double* tm = A.tmat + pw->tm_off[orient];
     int pc = 0, pm = 0;
-    double guess = __longlong_as_double(0x7ff8000000000000LL);  // NaN: no guess yet
+    const double NANV = __longlong_as_double(0x7ff8000000000000LL);
+    double guess = NANV;  // no guess yet
     const int i0 = rb * kSelRowsPerCta;
     for (int i = i0; i < imin(i0 + kSelRowsPerCta, Mo); ++i) {
         const double* row = tm + (int64_t)i * No;
@@ -331,7 +339,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
 #pragma unroll
         for (int e = 0; e < EPT; ++e) {
             const int j = tid + e * kSelThreads;
-            v[e] = (j < No) ? row[j] : INF;  // +inf pads: never counted (thresholds are finite)
+            v[e] = (j < No) ? row[j] : NANV;  // NaN pads: never <= a threshold, ignored by fmin / fmax
         }
         double sep;
         if (k <= 0) {
@@ -343,7 +351,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
 #pragma unroll
             for (int e = 0; e < EPT; ++e) {
                 lo = fmin(lo, v[e]);
-                if (v[e] < INF) hi = fmax(hi, v[e]);
+                hi = fmax(hi, v[e]);
             }
             cta_minmax(lo, hi, s_mm, pm, warp, lane);
             auto count_le = [&](double t) {
@@ -367,7 +375,8 @@ __global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
                             if (iter & 1)
                                 t = 0.5 * lo + 0.5 * hi;
                             else
-                                t = lo + (hi - lo) * ((double)(k - clo) / (double)(chi - clo));
+                                // the fraction only steers the search: single precision is plenty
+                                t = lo + (hi - lo) * (double)((float)(k - clo) * __frcp_rn((float)(chi - clo)));
                             if (!(t > lo && t < hi)) {
                                 t = 0.5 * lo + 0.5 * hi;
                                 if (!(t > lo && t < hi)) break;  // bracket collapsed: exact ties
@@ -405,6 +414,64 @@ __global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
         }
         guess = sep;
         if (tid == 0) A.seps[rsep_off + i] = sep;
+    }
+}
+
+// ---------------------------------------------------------------- CRP straight from the stored T matrix
+// When both orientations of a pair went through MODE 3 in the same wave, the CRP orientation's T matrix is
+// still in memory when its separators arrive: comparing it with them is one streaming pass (8 bytes in, 1 bit
+// out per cell) instead of a third sweep.  The stored T is exactly what a MODE 1 tile would recompute.
+struct EmitArgs {
+    const PairWork* pairs;
+    const uint32_t* items;  // pair
+    int n_items;
+    int row_blocks;
+    const double* tmat;
+    const double* seps;
+    uint32_t* crp;
+    int m;
+    uint32_t flags;
+};
+constexpr int kEmitThreads = 256;
+constexpr int kEmitRowsPerWarp = 4;
+
+__global__ void __launch_bounds__(kEmitThreads) k_emit_crp(EmitArgs A) {
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int it = (int)(blockIdx.x / (unsigned)A.row_blocks), rb = (int)(blockIdx.x % (unsigned)A.row_blocks);
+    if (it >= A.n_items) return;
+    const int pidx = (int)A.items[it];
+    const PairWork* pw = A.pairs + pidx;
+    const int orient = pw->swap;
+    const int Lr = orient ? pw->Lj : pw->Li, Lc = orient ? pw->Li : pw->Lj;
+    const int Mo = Lr - A.m + 1, No = Lc - A.m + 1;
+    if (Mo <= 0 || No <= 0) return;
+    const bool nonmutual = (A.flags & kFlagNonMutual) != 0;
+    const double* tm = A.tmat + pw->tm_off[orient];
+    const double* rsep = A.seps + pw->sep_off + (orient ? pw->M : 0);
+    const double* csep = A.seps + pw->sep_off + (orient ? 0 : pw->M);
+    const int wp = pw->crp_wp;
+    const int i0 = (rb * (kEmitThreads / 32) + warp) * kEmitRowsPerWarp;
+    for (int i = i0; i < imin(i0 + kEmitRowsPerWarp, Mo); ++i) {
+        const double rs = (nonmutual && orient) ? INF : rsep[i];
+        const double* row = tm + (int64_t)i * No;
+        uint32_t* out = A.crp + pw->crp_off + (int64_t)i * wp;
+        uint32_t mine = 0;
+        for (int w = 0; w < wp; ++w) {
+            const int j = 32 * w + lane;
+            bool bit = false;
+            if (j < No) {
+                const double t = row[j];
+                const double cs = (nonmutual && !orient) ? INF : csep[j];
+                bit = (t <= rs) && (t <= cs);
+            }
+            const uint32_t word = __ballot_sync(kFullMask, bit);
+            if ((w & 31) == lane) mine = word;
+            if ((w & 31) == 31 || w == wp - 1) {
+                const int wb = w & ~31;
+                if (wb + lane <= w) out[wb + lane] = mine;  // 32 words at a time, coalesced
+            }
+        }
     }
 }
 

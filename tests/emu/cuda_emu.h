@@ -414,6 +414,7 @@ inline float __fdiv_rn(float a, float b) { volatile float r = a / b; return r; }
 inline double __ddiv_rn(double a, double b) { volatile double r = a / b; return r; }
 inline float __fmul_rn(float a, float b) { volatile float r = a * b; return r; }
 inline float __fdividef(float a, float b) { return a / b; }
+inline float __frcp_rn(float a) { return 1.0f / a; }
 inline int __double2int_rn(double v) { return (int)std::nearbyint(v); }
 inline double __longlong_as_double(long long v) { return emu::from_bits<double>((uint64_t)v); }
 inline long long __double_as_longlong(double v) { return (long long)emu::to_bits(v); }
