@@ -609,6 +609,8 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         w.sep_off = sep_total;
         w.crp_off = crp_total;
         const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
+        if (br > 0 && std::min(w.crp_rows, w.crp_cols) > 32767)
+            return fail(ACOSS_ERR_ARG, "plot %d x %d: the DP hand-over packs Qmax values in 16 bits (min side <= 32767)", w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
         if (ok) {
@@ -1083,6 +1085,8 @@ int acoss_dp_packed(acoss_ctx* c, const uint32_t* crp, const int64_t* crp_offset
         w.crp_off = crp_total;
         crp_total += (int64_t)w.crp_rows * w.crp_wp;
         const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
+        if (br > 0 && std::min(w.crp_rows, w.crp_cols) > 32767)
+            return fail(ACOSS_ERR_ARG, "plot %d x %d: the DP hand-over packs Qmax values in 16 bits (min side <= 32767)", w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
         classify_dp(c, L, (uint32_t)b, w.crp_cols);
@@ -1161,6 +1165,8 @@ int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* c
         w.crp_wp = d.wp;
         w.crp_off = crp_total;
         const int64_t br = bnd_records(c, w.crp_rows, w.crp_cols);
+        if (br > 0 && std::min(w.crp_rows, w.crp_cols) > 32767)
+            return fail(ACOSS_ERR_ARG, "plot %d x %d: the DP hand-over packs Qmax values in 16 bits (min side <= 32767)", w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
         classify_dp(c, L, (uint32_t)b, w.crp_cols);

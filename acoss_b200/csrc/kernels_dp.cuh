@@ -46,7 +46,8 @@ __device__ __forceinline__ float sw_step(float h, float ms, unsigned here, unsig
 // One DP row for all three recurrences.  S1, S2, S3 are the register slots that hold rows i-1,
 // i-2, i-3; the new row overwrites slot S3 in place: cells are visited right to left, so a cell
 // reads its left neighbours of row i-3 before they are replaced (no register copies per row).
-template <int CPL, bool WITH_SW, int S1, int S2, int S3>
+// STEADY: the row index is known to be >= 3 (every row after the first group of three): no per-row predicates.
+template <int CPL, bool WITH_SW, int S1, int S2, int S3, bool STEADY>
 __device__ __forceinline__ void dp_row(int i, unsigned s0, unsigned sp1, unsigned sp2, int (&q)[3][CPL], int (&d)[3][CPL],
                                        float (&h)[3][CPL], int (&e)[CPL], int (&f)[CPL], int qL1, int qL2, int q2L1,
                                        int dL1, int dL2, int dL3, int d2L1, int d3L1, float hL1, float hL2, float h2L1,
@@ -61,7 +62,7 @@ __device__ __forceinline__ void dp_row(int i, unsigned s0, unsigned sp1, unsigne
         const int s2x = sv[c + 2];
         const int delta = s2x + (s2x >> 1) - 1;  // +2 on a match, -1 on a gap
         // ---- Qmax (SequenceAlignment.c:121-141)
-        if (i >= 2) {
+        if (STEADY || i >= 2) {
             const int p1 = (c >= 1) ? q[S1][c >= 1 ? c - 1 : 0] : qL1;
             const int p2 = (c >= 1) ? q[S2][c >= 1 ? c - 1 : 0] : q2L1;
             const int p3 = (c >= 2) ? q[S1][c >= 2 ? c - 2 : 0] : (c == 1 ? qL1 : qL2);
@@ -70,7 +71,7 @@ __device__ __forceinline__ void dp_row(int i, unsigned s0, unsigned sp1, unsigne
             q[S3][c] = 0;
         }
         // ---- Dmax (SequenceAlignment.c:155-177); e = 2 S[i-1][j], f = 2 (S[i-2][j] + S[i-1][j])
-        if (i >= 3) {
+        if (STEADY || i >= 3) {
             const int a1 = (c >= 1) ? d[S1][c >= 1 ? c - 1 : 0] : dL1;
             const int a2 = ((c >= 1) ? d[S2][c >= 1 ? c - 1 : 0] : d2L1) + e[c];
             const int a3 = ((c >= 2) ? d[S1][c >= 2 ? c - 2 : 0] : (c == 1 ? dL1 : dL2)) + sv[c + 1];
@@ -87,7 +88,7 @@ __device__ __forceinline__ void dp_row(int i, unsigned s0, unsigned sp1, unsigne
         e[c] = s2x;
         // ---- constrained Smith-Waterman (SequenceAlignment.c:83-97), 0-based on S
         if (WITH_SW) {
-            if (i >= 2) {
+            if (STEADY || i >= 2) {
                 const unsigned s = (s0 >> (c + 2)) & 1u;
                 const float ms = s ? 1.0f : -1.0f;
                 const unsigned b11 = (sp1 >> (c + 1)) & 1u;  // S[i-1][j-1]
@@ -108,11 +109,11 @@ __device__ __forceinline__ void dp_row(int i, unsigned s0, unsigned sp1, unsigne
     if (first_cols) {
         q[S3][0] = q[S3][1] = 0;
         d[S3][0] = d[S3][1] = 0;
-        d[S3][2] = (stale && i >= 2) ? sv[4] : 0;
+        d[S3][2] = (stale && (STEADY || i >= 2)) ? sv[4] : 0;
         if (WITH_SW) h[S3][0] = h[S3][1] = 0.0f;
     }
     // running maxima over real cells only
-    if (i >= 2) {
+    if (STEADY || i >= 2) {
         if (nvalid == CPL) {
 #pragma unroll
             for (int c = 0; c < CPL; ++c) {
@@ -128,7 +129,7 @@ __device__ __forceinline__ void dp_row(int i, unsigned s0, unsigned sp1, unsigne
                 }
         }
     }
-    if (i >= 3) {
+    if (STEADY || i >= 3) {
         if (nvalid == CPL && !first_cols) {
 #pragma unroll
             for (int c = 0; c < CPL; ++c) dbest = imax(dbest, d[S3][c]);
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(128, (CPL >= 16 ? 4 : 5)) k_dp(DpArgs A) {
         const bool first_cols = (j0 == 0);
         const bool write_bnd = bnd_out != nullptr && lane == 31 && blk + 1 < nblk;
 
-#define ACOSS_DP_ROW(S1, S2, S3, U)                                                                            \
+#define ACOSS_DP_ROW(S1, S2, S3, U, ST)                                                                          \
     {                                                                                                         \
         const unsigned s0 = __funnelshift_r(plo[U], phi[U], fsh) & fmask;                                     \
         int qL1 = __shfl_up_sync(kFullMask, q[S1][CPL - 1], 1);                                               \
@@ -194,22 +195,28 @@ __global__ void __launch_bounds__(128, (CPL >= 16 ? 4 : 5)) k_dp(DpArgs A) {
         if (lane == 0) {                                                                                      \
             qL1 = qL2 = dL1 = dL2 = dL3 = 0;                                                                  \
             hL1 = hL2 = 0.0f;                                                                                 \
-            if (blk > 0 && i > 0) {                                                                           \
-                const int4 ra = pra[U], rb = prb[U];                                                          \
-                qL1 = ra.x; qL2 = ra.y; dL1 = ra.z; dL2 = ra.w;                                               \
-                dL3 = rb.x; hL1 = __int_as_float(rb.y); hL2 = __int_as_float(rb.z);                           \
+            if (blk > 0 && (ST || i > 0)) {                                                                   \
+                const int4 ra = pra[U];                                                                       \
+                qL1 = ra.x & 0xffff; qL2 = (int)((unsigned)ra.x >> 16); dL1 = ra.y; dL2 = ra.z; dL3 = ra.w;   \
+                if (WITH_SW) {                                                                                \
+                    const int4 rb = prb[U];                                                                   \
+                    hL1 = __int_as_float(rb.x); hL2 = __int_as_float(rb.y);                                   \
+                }                                                                                             \
             }                                                                                                 \
         }                                                                                                     \
         const int q2L1 = cq1, d2L1 = cd1, d3L1 = cd2;                                                         \
         const float h2L1 = ch1;                                                                               \
         cq1 = qL1; cd2 = cd1; cd1 = dL1; ch1 = hL1;                                                           \
-        dp_row<CPL, WITH_SW, S1, S2, S3>(i, s0, sp1, sp2, q, d, h, e, f, qL1, qL2, q2L1, dL1, dL2, dL3, d2L1, \
+        dp_row<CPL, WITH_SW, S1, S2, S3, ST>(i, s0, sp1, sp2, q, d, h, e, f, qL1, qL2, q2L1, dL1, dL2, dL3, d2L1, \
                                          d3L1, hL1, hL2, h2L1, stale, first_cols, nvalid, j0, qbest, dbest,   \
                                          hbest);                                                              \
         if (write_bnd) {                                                                                      \
-            bnd_out[(int64_t)i * 2] = make_int4(q[S3][CPL - 1], q[S3][CPL - 2], d[S3][CPL - 1], d[S3][CPL - 2]); \
-            bnd_out[(int64_t)i * 2 + 1] = make_int4(d[S3][CPL - 3], __float_as_int(h[S3][CPL - 1]),           \
-                                                    __float_as_int(h[S3][CPL - 2]), 0);                       \
+            /* one record per row: Qmax values are < 2^16 half-units (plots of up to 32767 rows or columns) */ \
+            bnd_out[(int64_t)i * 2] = make_int4(q[S3][CPL - 1] | (q[S3][CPL - 2] << 16), d[S3][CPL - 1],      \
+                                                d[S3][CPL - 2], d[S3][CPL - 3]);                              \
+            if (WITH_SW)                                                                                      \
+                bnd_out[(int64_t)i * 2 + 1] = make_int4(__float_as_int(h[S3][CPL - 1]),                       \
+                                                        __float_as_int(h[S3][CPL - 2]), 0, 0);                \
         }                                                                                                     \
         sp2 = sp1;                                                                                            \
         sp1 = s0;                                                                                             \
@@ -233,7 +240,7 @@ __global__ void __launch_bounds__(128, (CPL >= 16 ? 4 : 5)) k_dp(DpArgs A) {
             pra[u] = prb[u] = make_int4(0, 0, 0, 0);
             if (rd_bnd && u >= 1 && u - 1 < rows) {
                 pra[u] = bnd_in[(int64_t)(u - 1) * 2];
-                prb[u] = bnd_in[(int64_t)(u - 1) * 2 + 1];
+                if (WITH_SW) prb[u] = bnd_in[(int64_t)(u - 1) * 2 + 1];
             }
         }
         for (int i0 = 0; i0 < rows; i0 += 3) {
@@ -246,15 +253,23 @@ __global__ void __launch_bounds__(128, (CPL >= 16 ? 4 : 5)) k_dp(DpArgs A) {
                 nra[u] = nrb[u] = make_int4(0, 0, 0, 0);
                 if (rd_bnd && in < rows) {
                     nra[u] = bnd_in[(int64_t)(in - 1) * 2];
-                    nrb[u] = bnd_in[(int64_t)(in - 1) * 2 + 1];
+                    if (WITH_SW) nrb[u] = bnd_in[(int64_t)(in - 1) * 2 + 1];
                 }
             }
             int i = i0;
-            ACOSS_DP_ROW(2, 1, 0, 0)
-            i = i0 + 1;
-            if (i < rows) ACOSS_DP_ROW(0, 2, 1, 1)
-            i = i0 + 2;
-            if (i < rows) ACOSS_DP_ROW(1, 0, 2, 2)
+            if (i0 >= 3) {
+                ACOSS_DP_ROW(2, 1, 0, 0, true)
+                i = i0 + 1;
+                if (i < rows) ACOSS_DP_ROW(0, 2, 1, 1, true)
+                i = i0 + 2;
+                if (i < rows) ACOSS_DP_ROW(1, 0, 2, 2, true)
+            } else {
+                ACOSS_DP_ROW(2, 1, 0, 0, false)
+                i = i0 + 1;
+                if (i < rows) ACOSS_DP_ROW(0, 2, 1, 1, false)
+                i = i0 + 2;
+                if (i < rows) ACOSS_DP_ROW(1, 0, 2, 2, false)
+            }
 #pragma unroll
             for (int u = 0; u < 3; ++u) {
                 plo[u] = nlo[u];
