@@ -112,6 +112,22 @@ __device__ __forceinline__ void dp_row(int i, unsigned s0, unsigned sp1, unsigne
         d[S3][2] = (stale && (STEADY || i >= 2)) ? sv[4] : 0;
         if (WITH_SW) h[S3][0] = h[S3][1] = 0.0f;
     }
+    // Steady rows: the maxima may run over the columns beyond the plot as well.  Those cells have S = 0 (fmask),
+    // so a Qmax cell there is max(0, max(predecessors) - 1) and a Dmax cell max(0, max5(...) - 1) where every
+    // bonus term comes with a valid matched cell of the same row that scores at least one half-unit more: by
+    // induction each such value is strictly below some real cell's, and the maximum is unchanged.
+    if (STEADY && !WITH_SW) {
+#pragma unroll
+        for (int c = 0; c < CPL; ++c) qbest = imax(qbest, q[S3][c]);
+        if (!first_cols) {
+#pragma unroll
+            for (int c = 0; c < CPL; ++c) dbest = imax(dbest, d[S3][c]);
+        } else {
+#pragma unroll
+            for (int c = 3; c < CPL; ++c) dbest = imax(dbest, d[S3][c]);  // columns 0..2 are the table's border
+        }
+        return;
+    }
     // running maxima over real cells only
     if (STEADY || i >= 2) {
         if (nvalid == CPL) {

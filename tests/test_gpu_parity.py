@@ -83,6 +83,27 @@ def test_stress_config_4096_frames(ctx):
     assert 0.02 < dens < 0.095
 
 
+def test_dp_ragged_shapes_vs_oracle(ctx):
+    """k_dp on plots whose last lane / last column block is ragged, dense enough that the Dmax bonus terms next
+    to the plot's right edge matter (the steady rows take their maxima over the padded columns too)."""
+    from oracle import dp
+    rng = np.random.default_rng(77)
+    shapes = [(40, c) for c in (4, 5, 6, 7, 9, 31, 33, 125, 126, 127, 129, 130, 131, 133, 255, 257, 383, 385)]
+    shapes += [(r, 130) for r in (4, 5, 6, 7, 8, 9, 10)] + [(300, 381), (129, 129), (6, 515)]
+    plots = [(rng.uniform(size=(M, N)) < dens).astype(np.uint8) for (M, N) in shapes for dens in (0.08, 0.5, 0.9)]
+    for cpl in (4, 8, 16):
+        ctx.set_option("dp_max_cpl", cpl)
+        try:
+            out = ctx.dp_packed(plots, want_sw=False)
+            outc = ctx.dp_packed(plots, flags=_native.FLAG_DMAX_CLEAN, want_sw=False)
+        finally:
+            ctx.set_option("dp_max_cpl", 4)
+        for b, B in enumerate(plots):
+            q, d = dp.qmax_dmax_serra09(B)
+            assert (out[b, 0], out[b, 1]) == (q, d), (cpl, B.shape, b % 3)
+            assert outc[b, 1] == dp.dmax_clean(B), (cpl, B.shape, b % 3)
+
+
 def test_mfcc_path_no_oti(ctx):
     # Serra09.py:177-184: 13 bins, no OTI / roll
     rng = np.random.default_rng(13)
