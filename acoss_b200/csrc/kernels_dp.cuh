@@ -176,8 +176,12 @@ __global__ void __launch_bounds__(128, (CPL >= 16 ? 4 : 5)) k_dp(DpArgs A) {
         const int nvalid = imax(0, imin(CPL, cols - j0));
         // bits of the field that map to real columns (field bit t <-> column j0-2+t)
         const int vb = cols - (j0 - 2);
-        const unsigned fmask =
+        unsigned fmask =
             ((1u << (CPL + 2)) - 1u) & (vb >= 32 ? 0xffffffffu : (vb <= 0 ? 0u : ((1u << vb) - 1u)));
+#ifndef ACOSS_EMU
+        // loop invariant, but ptxas rematerialises its 7 instructions in every row: pin it in a register
+        asm volatile("mov.b32 %0, %0;" : "+r"(fmask));
+#endif
         int4* bnd_out = (pw.bnd_off >= 0) ? A.bnd + pw.bnd_off + (int64_t)(blk & 1) * rows * 2 : nullptr;
         const int4* bnd_in = (pw.bnd_off >= 0) ? A.bnd + pw.bnd_off + (int64_t)((blk & 1) ^ 1) * rows * 2 : nullptr;
         int q[3][CPL], d[3][CPL], e[CPL], f[CPL];
