@@ -150,6 +150,7 @@ struct acoss_ctx {
                                    // (kernels_sweep2.cuh); 3: warp-specialised variant of 2 (kernels_sweep3.cuh)
     int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
     int opt_single_stream = 0;     // 1: no side stream (profiling / debugging)
+    int opt_eval_direct = 0;       // 1: cliques of more than 5 songs through the one-compare-per-member rank kernel
     int opt_tiled_wide = 1;        // 1: column songs beyond the fast kernels go through the tiled sweep
                                    // (kernels_sweep1t.cuh); 0: through the one-CTA general sweep (kernels_sweep.cuh)
     uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
@@ -1467,9 +1468,11 @@ int acoss_eval_ranks(acoss_ctx* c, const float* D, int64_t n, const int32_t* ord
     if (kmax <= 1) { ACOSS_LAUNCH(k_eval_ranks<1>, rows, kEvalThreads, 0, c->stream, A); }
     else if (kmax <= 2) { ACOSS_LAUNCH(k_eval_ranks<2>, rows, kEvalThreads, 0, c->stream, A); }
     else if (kmax <= 4) { ACOSS_LAUNCH(k_eval_ranks<4>, rows, kEvalThreads, 0, c->stream, A); }
-    else if (kmax <= 8) { ACOSS_LAUNCH(k_eval_ranks<8>, rows, kEvalThreads, 0, c->stream, A); }
-    else if (kmax <= 12) { ACOSS_LAUNCH(k_eval_ranks<12>, rows, kEvalThreads, 0, c->stream, A); }
-    else { ACOSS_LAUNCH(k_eval_ranks<kEvalMembers>, rows, kEvalThreads, 0, c->stream, A); }
+    else if (c->opt_eval_direct) {
+        if (kmax <= 8) { ACOSS_LAUNCH(k_eval_ranks<8>, rows, kEvalThreads, 0, c->stream, A); }
+        else if (kmax <= 12) { ACOSS_LAUNCH(k_eval_ranks<12>, rows, kEvalThreads, 0, c->stream, A); }
+        else { ACOSS_LAUNCH(k_eval_ranks<kEvalMembers>, rows, kEvalThreads, 0, c->stream, A); }
+    } else { ACOSS_LAUNCH(k_eval_ranks_bs, rows, kEvalThreads, 0, c->stream, A); }
     c->launches++;
     CU(cudaGetLastError());
     CU(cudaEventRecord(c->ev[1], c->stream));
@@ -1493,6 +1496,8 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
         c->opt_force_wide = value != 0;
     else if (n == "force_gscratch")
         c->opt_force_gscratch = value != 0;
+    else if (n == "eval_direct")
+        c->opt_eval_direct = value != 0;
     else if (n == "tiled_wide")
         c->opt_tiled_wide = value != 0;
     else if (n == "sweep_gen") {

@@ -125,4 +125,108 @@ __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks(EvalArgs A) {
     }
 }
 
+// Larger cliques: binary search instead of one compare per member.  The (<= 15) members of a pass are sorted by
+// (score ascending, clique position descending) -- the order in which a row element "beats" them -- so the set of
+// members an element beats is a prefix of that list; its length b is found by a 4-step binary search on the scores
+// (plus a short walk over members of exactly equal score), counted in a per-thread histogram column in shared
+// memory (conflict-free), and member s ends up with  sum_{b > s} hist[b]  elements in front of it.  About 21
+// instructions per element for any clique size, against 3 per member for the direct kernel.
+constexpr int kEvalBsMembers = 15;
+
+__global__ void __launch_bounds__(kEvalThreads) k_eval_ranks_bs(EvalArgs A) {
+    __shared__ float s_rawv[16], s_val[16];
+    __shared__ int s_rawp[16], s_pos[16], s_tot[16];
+    __shared__ int s_hist[16 * kEvalThreads];
+    const int p = (int)blockIdx.x;
+    if (p >= A.rows) return;
+    const int tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int i = A.order[p];
+    const int start = A.cstart[p], K = A.csize[p];
+    const int64_t n = A.n;
+    const float* __restrict__ row = A.D + (int64_t)i * n;
+    int32_t* raw = A.raw + A.out_off[p];
+    int32_t* out = A.out + A.out_off[p];
+    const int nm_all = K - 1;
+    for (int m0 = 0; m0 < nm_all; m0 += kEvalBsMembers) {
+        const int nm = imin(kEvalBsMembers, nm_all - m0);
+        __syncthreads();
+        if (tid < 16) {
+            float v = INFINITY;  // pads sort last and are never beaten
+            int q = -1;
+            if (tid < nm) {
+                const int t = m0 + tid;
+                q = start + t + ((start + t >= p) ? 1 : 0);
+                v = row[A.order[q]];
+            }
+            s_rawv[tid] = v;
+            s_rawp[tid] = q;
+            s_tot[tid] = 0;
+        }
+#pragma unroll
+        for (int b = 0; b < 16; ++b) s_hist[b * kEvalThreads + tid] = 0;
+        __syncthreads();
+        if (tid < 16) {
+            const float v = s_rawv[tid];
+            const int q = s_rawp[tid];
+            int r = 0;
+            for (int u = 0; u < 16; ++u) {
+                const float vu = s_rawv[u];
+                const int qu = s_rawp[u];
+                r += (vu < v || (vu == v && (qu > q || (qu == q && u < tid)))) ? 1 : 0;
+            }
+            s_val[r] = v;
+            s_pos[r] = q;
+        }
+        __syncthreads();
+        const float mmin = s_val[0];
+        for (int64_t j0 = (int64_t)tid; j0 < n; j0 += 4 * kEvalThreads) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t j = j0 + (int64_t)u * kEvalThreads;
+                v[u] = (j < n && j != i) ? __ldg(row + j) : -INFINITY;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float x = v[u];
+                if (!(x >= mmin) || x == -INFINITY) continue;  // below every member / the diagonal / past the row
+                int b = (s_val[7] < x) ? 8 : 0;
+                b += (s_val[b + 3] < x) ? 4 : 0;
+                b += (s_val[b + 1] < x) ? 2 : 0;
+                b += (s_val[b] < x) ? 1 : 0;
+                if (s_val[b] == x) {
+                    // equal scores: the element also beats the members that come later in the clique order
+                    const int pj = A.pos[j0 + (int64_t)u * kEvalThreads];
+                    while (b < 16 && s_val[b] == x && pj < s_pos[b]) ++b;
+                }
+                if (b) s_hist[b * kEvalThreads + tid] += 1;
+            }
+        }
+        __syncthreads();
+        // bucket totals: warp w sums buckets 2w and 2w + 1
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int b = 2 * warp + h;
+            int c = 0;
+#pragma unroll
+            for (int e = 0; e < kEvalThreads / 32; ++e) c += s_hist[b * kEvalThreads + lane + 32 * e];
+            c = warp_sum(c);
+            if (lane == 0) s_tot[b] = c;
+        }
+        __syncthreads();
+        if (tid < nm) {
+            int c = 0;
+            for (int b = tid + 1; b < 16; ++b) c += s_tot[b];
+            raw[m0 + tid] = 1 + c;
+        }
+    }
+    __syncthreads();
+    for (int t = tid; t < nm_all; t += kEvalThreads) {
+        const int r = raw[t];
+        int slot = 0;
+        for (int u = 0; u < nm_all; ++u) slot += (raw[u] < r) ? 1 : 0;
+        out[slot] = r;
+    }
+}
+
 }  // namespace acoss

@@ -183,6 +183,8 @@ int acoss_last_eval_ms(acoss_ctx* ctx, float* out);
  * "sweep_gen" (2 .. 6: which generation of the cross-similarity sweep runs where it applies;
  * default 6 = FP64 tensor-core sweep for column songs of up to 631 frames, warp-specialised
  * SIMT sweep up to 960, integer-key SIMT sweep up to 1320, general sweeps beyond),
+ * "eval_direct" (0/1, default 0: acoss_eval_ranks counts cliques of more than 5 songs with one compare per member
+ * instead of the binary search + histogram kernel),
  * "tiled_wide" (0/1, default 1: column songs beyond 1408 frames go through the tiled float64 sweep,
  * kernels_sweep1t.cuh; 0 = the one-CTA general sweep they are checked against),
  * "gap_units" (2 .. 2^24: safety gap, in key units, below which a separator is re-decided in

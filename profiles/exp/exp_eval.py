@@ -34,6 +34,13 @@ for _ in range(reps):
     ir, Ks, r = ctx.eval_ranks(None, cliques, device_ptr=Dd.data_ptr())
     ms.append(ctx.last_eval_ms())
 ker_ms = float(np.median(ms))
+ctx.set_option("eval_direct", 1)   # the one-compare-per-member kernel, for comparison
+ms_direct = []
+for _ in range(reps):
+    ird, _, _ = ctx.eval_ranks(None, cliques, device_ptr=Dd.data_ptr())
+    ms_direct.append(ctx.last_eval_ms())
+ctx.set_option("eval_direct", 0)
+assert all(np.array_equal(a, b) for a, b in zip(ir, ird))
 t0 = time.perf_counter()
 for _ in range(3):
     ir2, _, _ = ctx.eval_ranks(Dh.numpy(), cliques)
@@ -57,7 +64,7 @@ peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.dirn
 alg_bytes = rows * n * 4
 print(json.dumps({
     "metric": "getEvalStatistics rank rows/s (benchmark-subset shape)", "n_songs": n, "active_rows": rows,
-    "kernel_ms": ker_ms, "rows_per_s": rows / (ker_ms * 1e-3),
+    "kernel_ms": ker_ms, "kernel_ms_direct_variant": float(np.median(ms_direct)), "rows_per_s": rows / (ker_ms * 1e-3),
     "e2e_ms_host_matrix": e2e_ms, "e2e_rows_per_s": rows / (e2e_ms * 1e-3), "h2d_bytes": int(D.nbytes), "d2h_bytes": rows * 12 * 4,
     "roofline": {"bound": "hbm", "achieved": alg_bytes / (ker_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                  "frac": alg_bytes / (ker_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None},

@@ -98,6 +98,12 @@ def test_emu_eval_kernel():
         assert check_ctx_against_oracle(ctx, *random_case(rng, [3, 2, 2, 1, 1], levels=4)) == 7
         assert check_ctx_against_oracle(ctx, *random_case(rng, [37, 18, 17, 2, 1, 1, 1])) == 74
         assert check_ctx_against_oracle(ctx, *random_case(rng, [20, 5, 1], levels=7)) == 25
+        # the one-compare-per-member kernel for large cliques (default: binary search + histogram)
+        ctx.set_option("eval_direct", 1)
+        try:
+            assert check_ctx_against_oracle(ctx, *random_case(rng, [33, 13, 6, 1], levels=9)) == 52
+        finally:
+            ctx.set_option("eval_direct", 0)
         iranks, Ks, rows = ctx.eval_ranks(np.zeros((3, 3), np.float32), [[0], [1], [2]])
         assert rows == 0 and iranks == []
         with pytest.raises(_native.AcossError):
@@ -133,6 +139,11 @@ def test_gpu_eval_golden_and_random(gpu_ctx):
     assert check_ctx_against_oracle(gpu_ctx, *random_case(rng, [2] * 700 + [1] * 3)) == 1400
     assert check_ctx_against_oracle(gpu_ctx, *random_case(rng, [300, 40, 33, 17, 16, 2, 1], levels=50)) == 408
     assert check_ctx_against_oracle(gpu_ctx, *random_case(rng, [5] * 50 + [1] * 7, levels=3)) == 250
+    gpu_ctx.set_option("eval_direct", 1)
+    try:
+        assert check_ctx_against_oracle(gpu_ctx, *random_case(rng, [13] * 60 + [40, 7, 1], levels=30)) == 827
+    finally:
+        gpu_ctx.set_option("eval_direct", 0)
     assert gpu_ctx.last_eval_ms() > 0
 
 
