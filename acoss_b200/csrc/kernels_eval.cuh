@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks(EvalArgs A) {
 // memory (conflict-free), and member s ends up with  sum_{b > s} hist[b]  elements in front of it.  About 21
 // instructions per element for any clique size, against 3 per member for the direct kernel.
 constexpr int kEvalBsMembers = 15;
+constexpr int kEvalBsFlight = 8;  // row elements in flight per thread
 
 __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks_bs(EvalArgs A) {
     __shared__ float s_rawv[16], s_val[16];
@@ -179,15 +180,15 @@ __global__ void __launch_bounds__(kEvalThreads) k_eval_ranks_bs(EvalArgs A) {
         }
         __syncthreads();
         const float mmin = s_val[0];
-        for (int64_t j0 = (int64_t)tid; j0 < n; j0 += 4 * kEvalThreads) {
-            float v[4];
+        for (int64_t j0 = (int64_t)tid; j0 < n; j0 += kEvalBsFlight * kEvalThreads) {
+            float v[kEvalBsFlight];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kEvalBsFlight; ++u) {
                 const int64_t j = j0 + (int64_t)u * kEvalThreads;
                 v[u] = (j < n && j != i) ? __ldg(row + j) : -INFINITY;
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kEvalBsFlight; ++u) {
                 const float x = v[u];
                 if (!(x >= mmin) || x == -INFINITY) continue;  // below every member / the diagonal / past the row
                 int b = (s_val[7] < x) ? 8 : 0;
