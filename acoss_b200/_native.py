@@ -60,6 +60,7 @@ SIGNATURES = {
     "acoss_reset_counters": (None, [ctypes.c_void_p]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
+    "acoss_debug_sweep7_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
 }
 
 

@@ -20,91 +20,18 @@
 #include "kernels_sweep.cuh"
 #include "kernels_sweep1t.cuh"
 #include "kernels_sweep2.cuh"
-#include "kernels_sweep3.cuh"
 #include "kernels_sweep4.cuh"
 #include "kernels_sweep5.cuh"
 #include "kernels_sweep6.cuh"
 #include "kernels_feat.cuh"
 #include "kernels_eval.cuh"
 
-#ifdef ACOSS_EMU
-#define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
-    emu::launch(dim3((unsigned)(grid)), dim3((unsigned)(block)), (size_t)(smem), [&]() { kfn(__VA_ARGS__); })
-template <class F>
-static cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, F, int, size_t) {
-    *n = 1;
-    return cudaSuccess;
-}
-#else
-#define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) kfn<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
-#endif
+#include "ctx.h"
+#include "sweep7.h"
 
 using namespace acoss;
 
 namespace {
-
-thread_local std::string g_last_error;
-
-int fail(int code, const char* fmt, ...) {
-    char buf[512];
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(buf, sizeof(buf), fmt, ap);
-    va_end(ap);
-    g_last_error = buf;
-    return code;
-}
-
-#define CU(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t e_ = (call);                                                                   \
-        if (e_ != cudaSuccess)                                                                     \
-            return fail(ACOSS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
-    } while (0)
-
-struct DevBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t reserve(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-    }
-    template <class T>
-    T* as() const { return reinterpret_cast<T*>(p); }
-};
-
-struct PinBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t reserve(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMallocHost(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() {
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        cap = 0;
-    }
-    template <class T>
-    T* as() const { return reinterpret_cast<T*>(p); }
-};
 
 int neighbours(double kappa, int n) {
     // CRPUtils.py:188-193: int(np.round(kappa*n)) (round-half-even on the double product)
@@ -112,58 +39,6 @@ int neighbours(double kappa, int n) {
     return (int)kappa;
 }
 
-}  // namespace
-
-struct acoss_ctx {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    cudaStream_t stream2 = nullptr;  // side stream for the few long-song sweeps (general kernels), higher priority
-    cudaEvent_t ev_prep = nullptr, ev_side = nullptr;
-    int sm_count = 0;
-    int max_smem = 0;
-    // songs
-    DevBuf frames, norms, offs, gchroma;
-    std::vector<int64_t> h_offs;
-    std::vector<int32_t> h_len;
-    int n_songs = 0, bins = 0;
-    int64_t total_frames = 0;
-    bool has_gchroma = false;
-    // per-chunk scratch
-    DevBuf pairs, items, counters, seps, crp, bnd, qout, dout, swout, otiout, gscratch;
-    DevBuf dense_in, dense_desc, dense_starts;
-    DevBuf tmat;                                // tiled long-song sweep: float64 T matrices of the chunk
-    DevBuf lens, wnorm, wnmax, sepk, sepx, nb;  // gen-4 sweep: windowed norms, integer separators, nibble CRPs
-    int wnorm_m = -1;                           // window the wnorm buffer was computed for
-    PinBuf h_stage;
-    std::vector<uint32_t> h_crp;
-    // test/tuning knobs (acoss_set_option)
-    int opt_force_wide = 0;      // send every sweep item through the 256-thread kernels
-    int opt_force_gscratch = 0;  // ring + strip in global scratch even when shared memory would do
-    int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
-                                 // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
-    int opt_chunk_pairs = 1 << 18;
-    int opt_sweep_gen = 6;         // 6 (default): DMMA sweep (kernels_sweep6.cuh) for every orientation whose column
-                                   // song has <= 631 frames (m = 9, 12 bins), the rest as 5;
-                                   // 5: warp-specialised integer-key sweep (kernels_sweep5.cuh; falls back
-                                   // to 4 for windows other than 9 and column songs over 960 frames);
-                                   // 4: integer-key sweep (kernels_sweep4.cuh); 2: float64-selection sweep
-                                   // (kernels_sweep2.cuh); 3: warp-specialised variant of 2 (kernels_sweep3.cuh)
-    int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
-    int opt_single_stream = 0;     // 1: no side stream (profiling / debugging)
-    int opt_eval_direct = 0;       // 1: cliques of more than 5 songs through the one-compare-per-member rank kernel
-    int opt_tiled_wide = 1;        // 1: column songs beyond the fast kernels go through the tiled sweep
-                                   // (kernels_sweep1t.cuh); 0: through the one-CTA general sweep (kernels_sweep.cuh)
-    uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
-    // accounting
-    int64_t launches = 0;
-    float stage_ms[5] = {0, 0, 0, 0, 0};
-    bool have_stage_ms = false;
-    float eval_ms = -1.f;  // device time of the last k_eval_ranks launch
-    DevBuf eval_D;         // score matrix of acoss_eval_ranks when it arrives from the host
-    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-};
-
-namespace {
 
 constexpr int64_t kMaxChunkSepDoubles = (int64_t)1 << 28;  // 2 GiB
 constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
@@ -187,6 +62,8 @@ struct ItemLists {
     std::vector<uint32_t> g6_0[kS6Buckets], g6_2[kS6Buckets];  // gen-6 (DMMA) sweep by CTA size
     std::vector<uint32_t> g5_0[2], g5_2[2];                          // gen-5 sweep, 4 / 8 compute warps
     std::vector<uint32_t> g4_pack;                                   // pairs whose nibble CRP needs packing
+    std::vector<uint32_t> g7_0[kSweep7Buckets], g7_2[kSweep7Buckets];  // gen-7 sweep by column capacity
+    bool have_keys = false;                                          // some pair uses the integer-key sweeps
     std::vector<uint32_t> dp4, dp8, dp16;
     int wide0_w = 0, wide1_w = 0;
 };
@@ -267,42 +144,6 @@ int launch_sweep_fast(acoss_ctx* c, const uint32_t* d_items, int n_items, int bu
     A.Wmax = 4 * T;
     A.flags = flags;
     ACOSS_LAUNCH(kfn, grid, T, smem, c->stream, A);
-    c->launches++;
-    CU(cudaGetLastError());
-    return ACOSS_OK;
-}
-
-template <int BINS, int MODE>
-int launch_sweep_ws(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter,
-                    uint32_t flags) {
-    if (n_items <= 0) return ACOSS_OK;
-    auto kfn = (m == 9) ? k_sweep_ws<BINS, MODE, 9> : (m == 20 ? k_sweep_ws<BINS, MODE, 20> : k_sweep_ws<BINS, MODE, 0>);
-    const int TC = 32 * (bucket + 1);
-    const int NS = ws_sel_warps(TC);
-    const int TT = TC + 32 * NS;
-    const size_t smem = ws_smem_bytes(TC, m);
-    if (smem > (size_t)c->max_smem - 1024) return fail(ACOSS_ERR_ARG, "window m=%d too large for the fast sweep", m);
-    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, TT, smem));
-    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep_ws cannot be resident (threads %d, smem %zu B)", TT, smem);
-    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
-    SweepArgs A;
-    memset(&A, 0, sizeof(A));
-    A.frames = c->frames.as<double>();
-    A.norms = c->norms.as<double>();
-    A.offs = c->offs.as<int64_t>();
-    A.pairs = c->pairs.as<PairWork>();
-    A.items = d_items;
-    A.n_items = n_items;
-    A.counter = d_counter;
-    A.seps = c->seps.as<double>();
-    A.crp = c->crp.as<uint32_t>();
-    A.m = m;
-    A.R = 2 * NS;
-    A.Wmax = 4 * TC;
-    A.flags = flags;
-    ACOSS_LAUNCH(kfn, grid, TT, smem, c->stream, A);
     c->launches++;
     CU(cudaGetLastError());
     return ACOSS_OK;
@@ -584,6 +425,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
                           tile_smem_bytes(m, BINS) <= (size_t)c->max_smem - 1024 && n < (1 << (kTileItemBits - 1));
     const bool gen4_ok = c->opt_sweep_gen >= 4 && BINS == 12 && !c->opt_force_wide && s4_own_lanes(m) >= 16 &&
                          (size_t)s4_layout(32 * kFastBuckets, m, BINS).total <= (size_t)c->max_smem - 1024;
+    const bool g7_ok = c->opt_sweep_gen >= 7 && m == 9 && (BINS == 12 || BINS == 13) && !c->opt_force_wide;
     const bool noswap = (flags & kFlagNoSwap) != 0;
     const bool nonmutual = (flags & kFlagNonMutual) != 0;
     for (int p = 0; p < n; ++p) {
@@ -622,8 +464,16 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             const int dpo = w.swap, other = 1 - dpo;
             const int wB = 256 * kSweepCPL;
             auto Lc_of = [&](int o) { return o ? w.Li : w.Lj; };
-            if (gen4_ok && std::max(w.Li, w.Lj) <= s4_max_cols(m)) {
-                // gen 4: both orientations through the integer-key sweep (a warp contributes own4 columns)
+            // gen 7 per orientation where the column song fits; both orientations of a pair must be served by
+            // integer-key kernels (gens 4-7 share the separator format), which for 13 bins means gen 7 twice
+            auto b7 = [&](int Lc) {
+                const int b = sweep7_bucket_for(Lc);
+                return (g7_ok && b >= 0 && acoss_sweep7_smem(b, BINS, 2) <= (size_t)c->max_smem) ? b : -1;
+            };
+            const bool keys12 = gen4_ok && std::max(w.Li, w.Lj) <= s4_max_cols(m);
+            const bool keys7 = b7(w.Li) >= 0 && b7(w.Lj) >= 0;
+            if (keys12 || keys7) {
+                L.have_keys = true;
                 const int own4 = s4_own_cols(m);
                 const bool g5 = c->opt_sweep_gen >= 5 && m == 9;  // the warp-specialised kernels are built for m = 9
                 const int b0 = (Lc_of(other) - 1) / own4, b2 = (Lc_of(dpo) - 1) / own4;  // compute warps needed - 1
@@ -632,31 +482,37 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
                                 (size_t)s6_layout(512, BINS).total <= (size_t)c->max_smem - 1024;
                 auto use6 = [&](int Lc) { return g6 && Lc <= kS6MaxThreads - kS6Pad; };
                 if (!(nonmutual && dpo == 0)) {
-                    if (use6(Lc_of(other)))
+                    if (b7(Lc_of(other)) >= 0)
+                        L.g7_0[b7(Lc_of(other))].push_back((uint32_t)p * 2 + other);
+                    else if (use6(Lc_of(other)))
                         L.g6_0[s6_bucket_of(s6_threads_for(Lc_of(other)))].push_back((uint32_t)p * 2 + other);
                     else if (g5 && b0 < 8)
                         L.g5_0[b0 / 4].push_back((uint32_t)p * 2 + other);
                     else
                         L.g4_0[b0].push_back((uint32_t)p * 2 + other);
                 }
-                if (use6(Lc_of(dpo))) {
-                    const int t2 = s6_threads_for(Lc_of(dpo));
-                    L.g6_2[s6_bucket_of(t2)].push_back((uint32_t)p);
-                    w.nb_stride = t2 / 4;
-                } else if (g5 && b2 < 8) {
-                    L.g5_2[b2 / 4].push_back((uint32_t)p);
-                    w.nb_stride = 128 * (b2 / 4 + 1);
+                if (b7(Lc_of(dpo)) >= 0) {
+                    L.g7_2[b7(Lc_of(dpo))].push_back((uint32_t)p);  // writes packed CRP words itself
                 } else {
-                    L.g4_2[b2].push_back((uint32_t)p);
-                    w.nb_stride = 32 * (b2 + 1);
+                    if (use6(Lc_of(dpo))) {
+                        const int t2 = s6_threads_for(Lc_of(dpo));
+                        L.g6_2[s6_bucket_of(t2)].push_back((uint32_t)p);
+                        w.nb_stride = t2 / 4;
+                    } else if (g5 && b2 < 8) {
+                        L.g5_2[b2 / 4].push_back((uint32_t)p);
+                        w.nb_stride = 128 * (b2 / 4 + 1);
+                    } else {
+                        L.g4_2[b2].push_back((uint32_t)p);
+                        w.nb_stride = 32 * (b2 + 1);
+                    }
+                    L.g4_pack.push_back((uint32_t)p);
+                    w.nb_off = nb_total;
+                    nb_total += ((int64_t)w.crp_rows * w.nb_stride + 15) & ~(int64_t)15;
                 }
-                L.g4_pack.push_back((uint32_t)p);
-                w.nb_off = nb_total;
-                nb_total += ((int64_t)w.crp_rows * w.nb_stride + 15) & ~(int64_t)15;
                 classify_dp(c, L, (uint32_t)p, w.crp_cols);
                 continue;
             }
-            const bool fast_ok = !c->opt_force_wide && std::max((size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows), (size_t)ws_smem_bytes(32 * kFastBuckets, m)) <= (size_t)c->max_smem - 1024;
+            const bool fast_ok = !c->opt_force_wide && (size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows) <= (size_t)c->max_smem - 1024;
             // separators of orientation o through the general sweep: tiled (T matrix + row selection) or one CTA
             auto push_wide0 = [&](int o) {
                 const int Lc = Lc_of(o);
@@ -724,7 +580,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     CU(c->swout.reserve((size_t)n * sizeof(float)));
     CU(c->otiout.reserve((size_t)n * sizeof(int32_t)));
     CU(c->counters.reserve(kCounterSlots * sizeof(unsigned int)));
-    if (!L.g4_pack.empty()) {
+    if (L.have_keys) {
         CU(c->sepk.reserve((size_t)std::max<int64_t>(sep_total, 1) * sizeof(int32_t)));
         CU(c->sepx.reserve((size_t)std::max<int64_t>(sep_total, 1) * sizeof(double)));
         CU(c->nb.reserve((size_t)std::max<int64_t>(nb_total, 16)));
@@ -736,6 +592,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
     for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
     for (int b = 0; b < kG6Buckets; ++b) n_items += L.g6_0[b].size() + L.g6_2[b].size();
+    for (int b = 0; b < kSweep7Buckets; ++b) n_items += L.g7_0[b].size() + L.g7_2[b].size();
     CU(c->items.reserve(std::max<size_t>(n_items, 1) * sizeof(uint32_t)));
     // stage: [PairWork...][items...]
     const size_t pw_bytes = (size_t)n * sizeof(PairWork);
@@ -744,6 +601,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_stage.as<char>() + pw_bytes);
     size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16, pos = 0;
     size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
+    size_t o_g70[kSweep7Buckets], o_g72[kSweep7Buckets];
     auto put = [&](const std::vector<uint32_t>& v) {
         size_t at = pos;
         if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
@@ -765,6 +623,8 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     for (int b = 0; b < 2; ++b) o_g52[b] = put(L.g5_2[b]);
     for (int b = 0; b < kG6Buckets; ++b) o_g60[b] = put(L.g6_0[b]);
     for (int b = 0; b < kG6Buckets; ++b) o_g62[b] = put(L.g6_2[b]);
+    for (int b = 0; b < kSweep7Buckets; ++b) o_g70[b] = put(L.g7_0[b]);
+    for (int b = 0; b < kSweep7Buckets; ++b) o_g72[b] = put(L.g7_2[b]);
     CU(cudaMemcpyAsync(c->pairs.p, c->h_stage.p, pw_bytes, cudaMemcpyHostToDevice, c->stream));
     if (n_items)
         CU(cudaMemcpyAsync(c->items.p, hi, n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
@@ -783,7 +643,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         CU(cudaGetLastError());
     }
     int rc;
-    if (!L.g4_pack.empty()) {
+    if (L.have_keys) {
         // windowed norms for this m (once per upload / window) and the pairs' fixed-point exponents
         if (c->wnorm_m != m) {
             CU(c->wnorm.reserve((size_t)std::max<int64_t>(c->total_frames, 1) * sizeof(double)));
@@ -805,7 +665,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     // each a long CTA.  Launched alone they leave most SMs idle (profiles/r01_g: 27 % of a step), so
     // they run on a second, higher-priority stream, first, and the persistent CTAs of the main sweeps
     // take the SMs that are left.  The two families never share a pair.
-    bool side_work = !L.wide0.empty() || !L.wide1.empty() || !L.t3.empty() || !L.t1.empty(), main_work = !L.g4_pack.empty();
+    bool side_work = !L.wide0.empty() || !L.wide1.empty() || !L.t3.empty() || !L.t1.empty(), main_work = L.have_keys;
     for (int b = 0; b < kFastBuckets; ++b) side_work = side_work || !L.fast0[b].empty() || !L.fast2[b].empty();
     const bool side = side_work && main_work && !c->opt_single_stream;
     {
@@ -822,7 +682,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         // largest buckets first: their CTAs are the long ones
         if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)
-            if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 0> : launch_sweep_ws<BINS, 0>)(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+            if ((rc = launch_sweep_fast<BINS, 0>(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
         for (size_t wv = 0; wv < L.wave_t3.size(); ++wv) {
             const size_t a3 = L.wave_t3[wv], b3 = wv + 1 < L.wave_t3.size() ? L.wave_t3[wv + 1] : L.t3.size();
             const size_t as = L.wave_tsel[wv], bs = wv + 1 < L.wave_tsel.size() ? L.wave_tsel[wv + 1] : L.tsel.size();
@@ -835,9 +695,11 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         if ((rc = launch_sweep_tile<BINS, 1>(c, d_items + o_t1, (int)L.t1.size(), m, d_cnt + 73, flags))) return rc;
         if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)
-            if ((rc = (c->opt_sweep_gen != 3 ? launch_sweep_fast<BINS, 2> : launch_sweep_ws<BINS, 2>)(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
+            if ((rc = launch_sweep_fast<BINS, 2>(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
         if (side) CU(cudaEventRecord(c->ev_side, c->stream2));
     }
+    for (int b = kSweep7Buckets - 1; b >= 0; --b)
+        if ((rc = acoss_launch_sweep7(c, 0, BINS, d_items + o_g70[b], (int)L.g7_0[b].size(), b, d_cnt + 80 + b, flags))) return rc;
     for (int b = kG6Buckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep6<0>(c, d_items + o_g60[b], (int)L.g6_0[b].size(), b, m, d_cnt + 64 + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
@@ -845,6 +707,8 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     for (int b = kFastBuckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
+    for (int b = kSweep7Buckets - 1; b >= 0; --b)
+        if ((rc = acoss_launch_sweep7(c, 2, BINS, d_items + o_g72[b], (int)L.g7_2[b].size(), b, d_cnt + 80 + kSweep7Buckets + b, flags))) return rc;
     for (int b = kG6Buckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep6<2>(c, d_items + o_g62[b], (int)L.g6_2[b].size(), b, m, d_cnt + 64 + kG6Buckets + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
@@ -914,9 +778,14 @@ int check_ctx(acoss_ctx* c) {
 
 }  // namespace
 
+std::string& acoss_error_slot() {
+    thread_local std::string g_last_error;
+    return g_last_error;
+}
+
 extern "C" {
 
-const char* acoss_last_error(void) { return g_last_error.c_str(); }
+const char* acoss_last_error(void) { return acoss_error_slot().c_str(); }
 int acoss_version(void) { return 100; }
 
 int acoss_create(acoss_ctx** out, int device) {
@@ -1501,7 +1370,7 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
     else if (n == "tiled_wide")
         c->opt_tiled_wide = value != 0;
     else if (n == "sweep_gen") {
-        if (value < 2 || value > 6) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2 .. 6");
+        if (value < 2 || value > 7 || value == 3) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2, 4, 5, 6 or 7");
         c->opt_sweep_gen = (int)value;
     } else if (n == "gap_units") {
         if (value < 2 || value > (1 << 24)) return fail(ACOSS_ERR_ARG, "gap_units must be in [2, 2^24]");
@@ -1547,6 +1416,14 @@ int acoss_debug_sweep6_cycles(acoss_ctx* c, uint64_t out[8], int reset) {
     (void)reset;
 #endif
     return ACOSS_OK;
+}
+
+int acoss_debug_sweep7_stats(acoss_ctx* c, uint64_t out[8], int reset) {
+    if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
+    unsigned long long h[8];
+    const int rc = acoss_sweep7_stats(c, h, reset);
+    for (int i = 0; i < 8; ++i) out[i] = h[i];
+    return rc;
 }
 
 int acoss_last_stage_ms(acoss_ctx* c, float out[5]) {

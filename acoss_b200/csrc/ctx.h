@@ -1,0 +1,140 @@
+// ctx.h -- the library context and the small host helpers shared by the translation units of
+// libacoss_b200.so (api.cu: the C ABI; sweep7.cu: the default sweep kernels and their launcher).
+#pragma once
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/acoss_b200.h"
+#include "common.cuh"
+
+#ifdef ACOSS_EMU
+#define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) \
+    emu::launch(dim3((unsigned)(grid)), dim3((unsigned)(block)), (size_t)(smem), [&]() { kfn(__VA_ARGS__); })
+template <class F>
+static cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, F, int, size_t) {
+    *n = 1;
+    return cudaSuccess;
+}
+#else
+#define ACOSS_LAUNCH(kfn, grid, block, smem, stream, ...) kfn<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#endif
+
+std::string& acoss_error_slot();  // thread-local last error (api.cu)
+
+inline int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    acoss_error_slot() = buf;
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(ACOSS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+
+struct acoss_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;  // side stream for the few long-song sweeps (general kernels), higher priority
+    cudaEvent_t ev_prep = nullptr, ev_side = nullptr;
+    int sm_count = 0;
+    int max_smem = 0;
+    // songs
+    DevBuf frames, norms, offs, gchroma;
+    std::vector<int64_t> h_offs;
+    std::vector<int32_t> h_len;
+    int n_songs = 0, bins = 0;
+    int64_t total_frames = 0;
+    bool has_gchroma = false;
+    // per-chunk scratch
+    DevBuf pairs, items, counters, seps, crp, bnd, qout, dout, swout, otiout, gscratch;
+    DevBuf dense_in, dense_desc, dense_starts;
+    DevBuf tmat;                                // tiled long-song sweep: float64 T matrices of the chunk
+    DevBuf lens, wnorm, wnmax, sepk, sepx, nb;  // gen-4 sweep: windowed norms, integer separators, nibble CRPs
+    int wnorm_m = -1;                           // window the wnorm buffer was computed for
+    PinBuf h_stage;
+    std::vector<uint32_t> h_crp;
+    // test/tuning knobs (acoss_set_option)
+    int opt_force_wide = 0;      // send every sweep item through the 256-thread kernels
+    int opt_force_gscratch = 0;  // ring + strip in global scratch even when shared memory would do
+    int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
+                                 // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
+    int opt_chunk_pairs = 1 << 18;
+    int opt_sweep_gen = 7;         // 7 (default): lane-group selection + packed CRP from the sweep (kernels_sweep7.cuh)
+                                   // for every orientation whose column song has <= 1015 frames (m = 9, 12 / 13
+                                   // bins), the rest as 6;
+                                   // 6: DMMA sweep (kernels_sweep6.cuh) for every orientation whose column
+                                   // song has <= 631 frames (m = 9, 12 bins), the rest as 5;
+                                   // 5: warp-specialised integer-key sweep (kernels_sweep5.cuh; falls back
+                                   // to 4 for windows other than 9 and column songs over 960 frames);
+                                   // 4: integer-key sweep (kernels_sweep4.cuh); 2: float64-selection sweep
+                                   // (kernels_sweep2.cuh)
+    int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
+    int opt_single_stream = 0;     // 1: no side stream (profiling / debugging)
+    int opt_eval_direct = 0;       // 1: cliques of more than 5 songs through the one-compare-per-member rank kernel
+    int opt_tiled_wide = 1;        // 1: column songs beyond the fast kernels go through the tiled sweep
+                                   // (kernels_sweep1t.cuh); 0: through the one-CTA general sweep (kernels_sweep.cuh)
+    uint32_t opt_debug_flags = 0;  // OR-ed into the kernel flags (profiling experiments only)
+    // accounting
+    int64_t launches = 0;
+    float stage_ms[5] = {0, 0, 0, 0, 0};
+    bool have_stage_ms = false;
+    float eval_ms = -1.f;  // device time of the last k_eval_ranks launch
+    DevBuf eval_D;         // score matrix of acoss_eval_ranks when it arrives from the host
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+

@@ -158,7 +158,7 @@ __device__ __forceinline__ unsigned s4_umax(unsigned a, unsigned b) { return a >
 // sum over the window of |roll(x_i, oti) - y_j|^2 (Serra09.py:166-170), rows = song_i windows.
 // Used only for the few cells of "unsafe" rows; never inlined so that producer and consumer
 // execute the same instruction sequence.
-__device__ __noinline__ double s4_cell_exact(const double* __restrict__ fi, const double* __restrict__ fj, int bins,
+static __device__ __noinline__ double s4_cell_exact(const double* __restrict__ fi, const double* __restrict__ fj, int bins,
                                              int oti, int m, int wi, int wj) {
     double acc = 0.0;
     for (int q = 0; q < m; ++q) {
@@ -597,7 +597,7 @@ struct S4Pair {
     const double* fj;
     int bins, oti, m, orient;
 };
-__device__ __noinline__ bool s4_resolve_unsafe(const uint4* __restrict__ row4, int nq, int k, int vk, int vk1,
+static __device__ __noinline__ bool s4_resolve_unsafe(const uint4* __restrict__ row4, int nq, int k, int vk, int vk1,
                                                const S4Pair& pp, int irow, int mwin, int lane, int* cand_cols,
                                                int* cand_cnt, double& sepx, int& n_cand, unsigned& in_mask) {
     const int blo = vk - 2, bhi = vk1 + 2;
@@ -1201,7 +1201,7 @@ __global__ void ACOSS_MAXNREG4(168) k_sweep4(Sweep4Args A) {
 // ---------------------------------------------------------------- helpers around the sweep
 // One CTA per song: windowed squared norms wnorm[f] = sum of norms of the m frames ending at f
 // (0 for the first m-1 frames of a song) and the song's maximum.
-__global__ void __launch_bounds__(128) k_wnorm(const double* __restrict__ norms, const int64_t* __restrict__ offs,
+static __global__ void __launch_bounds__(128) k_wnorm(const double* __restrict__ norms, const int64_t* __restrict__ offs,
                                                const int32_t* __restrict__ lens, int n_songs, int m,
                                                double* __restrict__ wnorm, double* __restrict__ wnmax) {
     __shared__ double s_max[4];
@@ -1228,7 +1228,7 @@ __global__ void __launch_bounds__(128) k_wnorm(const double* __restrict__ norms,
 }
 
 // One thread per pair: the fixed-point exponent e (odd, 2^e > 4 (wmax_i + wmax_j)).
-__global__ void __launch_bounds__(128) k_expo(PairWork* __restrict__ pairs, int n_pairs,
+static __global__ void __launch_bounds__(128) k_expo(PairWork* __restrict__ pairs, int n_pairs,
                                               const double* __restrict__ wnmax) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pairs) return;
@@ -1242,7 +1242,7 @@ __global__ void __launch_bounds__(128) k_expo(PairWork* __restrict__ pairs, int 
 
 // One CTA per pair: nibble bytes (frame-column space) -> packed CRP words shifted by m-1
 // (bit t of word w of row r = CRP[r][32 w + t], the layout of the DP kernel and the debug dump).
-__global__ void __launch_bounds__(128) k_nb_to_packed(const PairWork* __restrict__ pairs, const uint32_t* __restrict__ items,
+static __global__ void __launch_bounds__(128) k_nb_to_packed(const PairWork* __restrict__ pairs, const uint32_t* __restrict__ items,
                                                       int n_items, const uint8_t* __restrict__ nb, uint32_t* __restrict__ crp,
                                                       int m) {
     const int it = blockIdx.x;

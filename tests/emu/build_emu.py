@@ -17,7 +17,7 @@ OUT = os.path.join(HERE, "_build", "libacoss_emu.so")
 
 
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "cuda_emu.h"),
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if not f.startswith("_")] + [os.path.join(HERE, "cuda_emu.h"),
                                                                 os.path.join(ROOT, "include", "acoss_b200.h")]
     if not force and os.path.exists(OUT) and all(os.path.getmtime(s) <= os.path.getmtime(OUT) for s in srcs):
         return OUT
@@ -25,8 +25,9 @@ def build(force: bool = False) -> str:
     cxx = shutil.which("g++")
     if cxx is None:
         raise RuntimeError("g++ not found")
-    cmd = [cxx, "-std=c++17", "-O1", "-g", "-shared", "-fPIC", "-x", "c++", "-DACOSS_EMU", "-I", HERE, "-I", CSRC,
-           os.path.join(CSRC, "api.cu"), "-o", OUT]
+    units = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
+    cmd = [cxx, "-std=c++17", "-O1", "-g", "-shared", "-fPIC", "-x", "c++", "-DACOSS_EMU", "-I", HERE, "-I", CSRC] + units + [
+        "-o", OUT]
     subprocess.check_call(cmd)
     return OUT
 

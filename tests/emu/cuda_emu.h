@@ -29,7 +29,7 @@
 #define __device__
 #define __host__
 #define __forceinline__ inline
-#define __noinline__
+#define __noinline__ inline
 #define __restrict__
 #define __launch_bounds__(...)
 #define __shared__ static
@@ -427,6 +427,8 @@ template <class T>
 inline T atomicMax(T* p, T v) { T o = *p; if (v > o) *p = v; return o; }
 template <class T>
 inline T atomicOr(T* p, T v) { T o = *p; *p = o | v; return o; }
+template <class T>
+inline T atomicAnd(T* p, T v) { T o = *p; *p = o & v; return o; }
 
 using std::max;
 using std::min;

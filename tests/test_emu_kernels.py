@@ -97,7 +97,7 @@ def test_emu_integer_key_sweeps(ctx):
     songs += synth.make_song_set("covers80", seed=34, n_songs=2, length_range=(500, 560))[0]
     pairs = np.array([(0, 1), (1, 2), (2, 3), (3, 4), (4, 0), (5, 6), (6, 2)], np.int32)
     try:
-        for gen in (4, 5, 6):
+        for gen in (4, 5, 6, 7):
             ctx.set_option("sweep_gen", gen)
             for gap in (2, 4096):
                 ctx.set_option("gap_units", gap)
@@ -106,7 +106,7 @@ def test_emu_integer_key_sweeps(ctx):
         ctx.set_option("gap_units", 2)
         pc.check_against_oracle(ctx, songs, pairs[:4], m=5, kappa=0.1, flags=_native.FLAG_NO_SWAP)
     finally:
-        ctx.set_option("sweep_gen", 6)
+        ctx.set_option("sweep_gen", 7)
         ctx.set_option("gap_units", 2)
 
 

@@ -160,7 +160,7 @@ def test_sweep_generations_agree_and_exact_path(ctx):
     try:
         ctx.set_option("sweep_gen", 2)
         base = ctx.serra09_pairs(pairs, want_crp=True)
-        for gen in (4, 5, 6):
+        for gen in (4, 5, 6, 7):
             for gap in (2, 256, 1 << 14, 1 << 18):
                 ctx.set_option("sweep_gen", gen)
                 ctx.set_option("gap_units", gap)
@@ -171,7 +171,7 @@ def test_sweep_generations_agree_and_exact_path(ctx):
                     assert np.array_equal(a, b), where + ": %d CRP bits differ" % int((a != b).sum())
                 assert np.array_equal(r["qmax_raw"], base["qmax_raw"]) and np.array_equal(r["dmax_raw"], base["dmax_raw"]), where
     finally:
-        ctx.set_option("sweep_gen", 6)
+        ctx.set_option("sweep_gen", 7)
         ctx.set_option("gap_units", 2)
     # and the default configuration against the oracle on the same pairs
     n, tied = pc.check_against_oracle(ctx, songs, pairs[:10], flags=_native.FLAG_NO_SWAP)
@@ -187,11 +187,11 @@ def test_generations_agree_at_full_size(ctx):
     ctx.upload_songs(songs)
     out = {}
     try:
-        for gen in (2, 4, 5, 6):
+        for gen in (2, 4, 5, 6, 7):
             ctx.set_option("sweep_gen", gen)
             out[gen] = ctx.serra09_pairs(pairs)
     finally:
-        ctx.set_option("sweep_gen", 6)
-    for gen in (4, 5, 6):
+        ctx.set_option("sweep_gen", 7)
+    for gen in (4, 5, 6, 7):
         assert np.array_equal(out[gen]["qmax_raw"], out[2]["qmax_raw"]), gen
         assert np.array_equal(out[gen]["dmax_raw"], out[2]["dmax_raw"]), gen
