@@ -44,6 +44,10 @@ def _defines():
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    tag = ",".join(_defines())
+    tagfile = os.path.join(OBJ, "defines.txt")
+    if os.path.exists(OUT) and os.path.exists(tagfile) and open(tagfile).read() != tag:
+        force = True  # built with other -D options
     if not force and up_to_date():
         return OUT
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
@@ -53,10 +57,6 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc not found and no prebuilt %s" % OUT)
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
     os.makedirs(OBJ, exist_ok=True)
-    tag = ",".join(_defines())
-    tagfile = os.path.join(OBJ, "defines.txt")
-    if not os.path.exists(tagfile) or open(tagfile).read() != tag:
-        force = True
     hdr_time = max(os.path.getmtime(h) for h in headers())
     jobs = []
     for cu in units():

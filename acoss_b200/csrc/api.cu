@@ -1418,11 +1418,11 @@ int acoss_debug_sweep6_cycles(acoss_ctx* c, uint64_t out[8], int reset) {
     return ACOSS_OK;
 }
 
-int acoss_debug_sweep7_stats(acoss_ctx* c, uint64_t out[8], int reset) {
+int acoss_debug_sweep7_stats(acoss_ctx* c, uint64_t out[16], int reset) {
     if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
-    unsigned long long h[8];
+    unsigned long long h[16];
     const int rc = acoss_sweep7_stats(c, h, reset);
-    for (int i = 0; i < 8; ++i) out[i] = h[i];
+    for (int i = 0; i < 16; ++i) out[i] = h[i];
     return rc;
 }
 

@@ -41,6 +41,15 @@
 
 namespace acoss {
 
+#if defined(ACOSS_S7_STATS) && !defined(ACOSS_EMU)
+// selection statistics (profiling builds): [0] s4_select calls, [1] counting passes, [2] walks, [3] walks that failed,
+// [4] boundary passes, [5] rows that left the main loop unresolved (bisection), [6] estimator calls, [7] no-guess starts
+static __device__ unsigned long long g_s4_sel_stats[8];
+#define S4_STAT(k) if (lane == 0) atomicAdd(&g_s4_sel_stats[k], 1ull)
+#else
+#define S4_STAT(k)
+#endif
+
 constexpr int kS4Stage = 32;        // rows of the row song per TMA bulk copy
 constexpr int kS4MaxWarps = 11;     // CTAs of up to 352 threads
 constexpr int kS4EMax = 6;          // ranks walked by the extraction pass
@@ -199,6 +208,22 @@ struct S4Keys {
             }
         }
     }
+    // Strided assignment: lane l holds columns l, l + 32, l + 64, ...  Neighbouring columns have similar distances
+    // (the songs are smooth), so with four consecutive columns per lane the few keys next to the separator cluster in
+    // one lane and the two-deep candidate walk runs dry (measured: 35 % of the walks); far-apart columns do not.
+    __device__ __forceinline__ void load_strided(const int* __restrict__ row, int lane) {
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            k[q].x = (unsigned)row[lane + 32 * (4 * q)];
+            k[q].y = (unsigned)row[lane + 32 * (4 * q + 1)];
+            k[q].z = (unsigned)row[lane + 32 * (4 * q + 2)];
+            k[q].w = (unsigned)row[lane + 32 * (4 * q + 3)];
+            if (kPacked) {
+                nk[kPacked ? 2 * q : 0] = __vneg2(__byte_perm(k[q].x, k[q].y, 0x7632));
+                nk[kPacked ? 2 * q + 1 : 0] = __vneg2(__byte_perm(k[q].z, k[q].w, 0x7632));
+            }
+        }
+    }
     __device__ __forceinline__ uint4 get(int q) const { return k[q]; }
     __device__ __forceinline__ int nq() const { return NQ; }
     // number of keys whose upper half is <= t15 (0 <= t15 <= 32766): one DPX op + one packed add per TWO keys
@@ -327,7 +352,9 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
     bool real_lo = false, real_hi = false;
     int t = t0;
     const int nq = keys.nq();
+    S4_STAT(0);
     if (!have_guess) {
+        S4_STAT(7);
         // no guess yet: bracket by the row's extremes
         unsigned mn = 0xffffffffu, mx = 0u;
 #pragma unroll
@@ -367,6 +394,7 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
         } else {
             c = s4_count(keys, t, lane);
         }
+        S4_STAT(1);
         if (haveA && c != cA) {
             const float sp = fabsf((float)(t - tA)) * __fdividef(1.0f, fabsf((float)(c - cA)));
             if (sp >= 1.0f) spacing = sp;
@@ -376,6 +404,7 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
         haveA = true;
         const int e = k - c;
         if (e == 0) {
+            S4_STAT(4);
             s4_boundary(keys, t, vk, vk1);
             done = true;
             break;
@@ -388,6 +417,8 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
         if (e > 0 && e <= kS4EMax) {
             unsigned oa, ob;
             const bool ok = s4_walk<true>(keys, (unsigned)t + 1u, e + 1, lane, oa, ob);
+            S4_STAT(2);
+            if (!(ok && oa < 0x80000000u)) { S4_STAT(3); }
             if (ok && oa < 0x80000000u) {
                 vk = (int)((unsigned)t + 1u + oa);
                 vk1 = (ob >= 0x80000000u) ? kKeyInf : (int)((unsigned)t + 1u + ob);
@@ -398,6 +429,8 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
         } else if (e < 0 && -e <= kS4EMax) {
             unsigned oa, ob;
             const bool ok = s4_walk<false>(keys, (unsigned)t, -e + 1, lane, oa, ob);
+            S4_STAT(2);
+            if (!(ok && ob < 0x80000000u)) { S4_STAT(3); }
             if (ok && ob < 0x80000000u) {
                 vk1 = t - (int)oa;
                 vk = t - (int)ob;
@@ -446,6 +479,7 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
         }
     }
     if (!done) {
+        S4_STAT(5);
         // plain bisection for the smallest t with count(<= t) >= k, then its successor
         int l = -1, h = kKeyInf - 1;
         if (real_lo) l = lo;
@@ -473,6 +507,7 @@ __device__ __forceinline__ void s4_select(const K& keys, int k, int nvalid, int 
 // is no such value.
 template <class K>
 __device__ __forceinline__ int s4_estimate(const K& keys, int jrank, int lane) {
+    S4_STAT(6);
     unsigned a1 = 0xffffffffu, a2 = 0xffffffffu, b1 = 0xffffffffu, b2 = 0xffffffffu;
     const int nq = keys.nq();
 #pragma unroll

@@ -7,15 +7,15 @@
 // row's selection = ~800 dependent warp instructions, 6 200 of the 12 200 cycles of a 16-row
 // period, barrier stalls 25-42 %):
 //
-//   * SELECTION IN LANE GROUPS.  A strip of R = 32..64 rows of keys is kept in shared memory and
-//     a row is resolved by a group of LPR = 8 (16) lanes, four (two) rows per warp in ONE
-//     instruction stream: every lane streams NC / LPR keys of its row per counting pass
-//     (LDS.128 + 2 integer instructions per key, no dependency between keys), the partial counts
-//     meet in log2(LPR) shuffles, and the threshold search (bracket + interpolation, the state
-//     is replicated in the group's lanes) runs once per pass for four rows.  Groups fetch rows
-//     from a shared counter, so a row that needs more passes holds up nobody.  The last pass of
-//     a row also tracks the largest key below and the smallest key above the threshold, which
-//     are the k-th and (k+1)-th keys: no candidate walk.
+//   * SELECTION IN CHAINS OF CONSECUTIVE ROWS.  A strip of R = 32..64 rows of keys is kept in shared
+//     memory and warp w resolves rows w R/NW .. (w+1) R/NW - 1 one after the other, the row's keys in
+//     registers.  Row r+1 of the matrix is row r shifted by one column plus one new frame, so the
+//     separator of row r is an excellent first threshold for row r+1 (measured on the bench songs: the
+//     count at that threshold is within 6 ranks of k for 68 % of the rows, median error 3 ranks, against
+//     a median error of 25-38 ranks for a separator 16-64 rows back, which is what gens 4-6 used): one
+//     counting pass and one candidate walk (s4_select / s4_walk of kernels_sweep4.cuh) resolve most
+//     rows.  The first row of a chain starts from the order-statistic estimate of its own keys
+//     (s4_estimate).  Every warp has the same number of rows, so the strip needs one barrier.
 //   * 8-ROW PERIODS.  The DMMA slab is 8 rows (one m8n8k4 tile row) and double buffered where
 //     shared memory allows, which leaves room for the strip.
 //   * PACKED CRP FROM THE SWEEP.  MODE 2 turns a strip into CRP words with one __ballot_sync per
@@ -34,11 +34,13 @@ namespace acoss {
 
 constexpr int kS7Pad = 9;      // NC >= Lc + kS7Pad zero columns flush the window (m <= 9)
 constexpr int kS7Per = 8;      // rows per period (one DMMA tile row)
-constexpr int kS7FullW = 6;    // bracket width (ranks) from which the passes also track the boundary keys
 
 #if defined(ACOSS_S7_STATS) && !defined(ACOSS_EMU)
 #define ACOSS_S7_STAT 1
-__device__ unsigned long long g_s7_stats[8];  // [0] rows, [1] count passes, [2] full passes, [3] unsafe rows
+// [0] rows resolved, [1] unsafe rows, [2] strips, [3] items; [4 + k] cycles of lane 0 of every warp in phase k:
+// 0 item setup, 1 stage 1, 2 stage 2, 3 period barrier, 4 strip init + barrier, 5 selection, 6 barrier behind the
+// selection, 7 export / ballots, 8 flag scan + float64 fix-ups, 9 CRP copy-out, 10 last barrier of the strip, 11 item fetch
+__device__ unsigned long long g_s7_stats[16];
 #else
 #define ACOSS_S7_STAT 0
 #endif
@@ -48,13 +50,16 @@ struct S7Cfg {
     static constexpr int NT = NT_, CPT = CPT_;
     static constexpr int NC = NT * CPT;                    // padded columns
     static constexpr int NW = NT / 32;
-    static constexpr int LPR = NC >= 1024 ? 16 : 8;        // lanes per row in the selection
-    static constexpr int NQ = NC / (4 * LPR);              // uint4 per lane and pass
-    static constexpr int R = NC <= 512 ? 64 : (NC <= 768 ? 48 : 32);  // rows per strip
-    static constexpr bool DBS = NC <= 512;                 // double-buffered slab
+    static constexpr int NQ = NC / 128;                    // uint4 of a strip row per lane (selection: keys in registers)
+    // NC = 512 as 256 threads x 2 diagonals: two CTAs per SM (independent barrier domains), 32-row strips, one slab
+    static constexpr bool TWO = (NT == 256 && CPT == 2);
+    static constexpr int R = TWO ? 32 : (NC <= 512 ? 64 : (NC <= 768 ? 48 : 32));  // rows per strip
+    static constexpr bool DBS = NC <= 512 && !TWO;         // double-buffered slab
+    static constexpr int MINB = TWO ? 2 : (NC <= 128 ? 4 : (NC <= 256 ? 2 : 1));
     static constexpr int LCP = NC + 8;                     // slab row stride (doubles), = 8 mod 16
     static constexpr int WPR = NC / 32;                    // CRP words per strip row
-    static_assert(NT % 32 == 0 && NC % 128 == 0 && R % (2 * kS7Per) == 0, "shape");
+    static constexpr int RPW = R / NW;                     // rows per warp: the chain resolved with lag-1 guesses
+    static_assert(NT % 32 == 0 && NC % 128 == 0 && R % (2 * kS7Per) == 0 && R % NW == 0, "shape");
 };
 
 __host__ __device__ constexpr int s7_capacity_threads(int cap) {  // column capacity -> threads
@@ -88,9 +93,9 @@ __host__ __device__ inline S7Layout s7_layout(int bins, int mode) {
     L.strip = o; o += C::R * C::NC * 4;
     L.csk = o;   o += (mode == 2 ? C::NC * 4 : 0);
     L.bits = o;  o += (mode == 2 ? C::R * C::WPR * 4 : 0);
-    L.rinfo = o; o += 6 * C::R * 4;                      // thr, kwx, vk, vk1, blo, flag
+    L.rinfo = o; o += 4 * C::R * 4;                      // thr, kwx, blo, flag
     L.cand = o;  o += C::NW * (kS4MaxFlag + 1) * 4;      // per warp: candidate columns + their count
-    L.misc = o;  o += (16 + C::R) * 4;                   // counters + the list of unsafe rows
+    L.misc = o;  o += 32 * 4;                            // [0] item, [5] flagged-column mark, [6] flagged row in the strip, [16..31] phase cycles
     o = (o + 7) & ~7;
     L.mbar = o;  o += 2 * 8;
     L.total = (o + 15) & ~15;
@@ -119,158 +124,6 @@ __device__ __forceinline__ void s7_dmma(double& c0, double& c1, double a, double
 #endif
 }
 
-// ---------------------------------------------------------------- selection
-// One pass of a lane over its share of a strip row: the number of keys > t and (FULL) the smallest
-// t - key >= 0 and the largest t - key < 0 as unsigned numbers, combined over the group's LPR lanes.
-template <int LPR, int NQ, bool FULL>
-__device__ __forceinline__ void s7_pass(const uint4* __restrict__ rq, int t, unsigned& gt, unsigned& dmin, unsigned& dmax) {
-    unsigned s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-    unsigned mn = 0xffffffffu, mx = 0u;
-#pragma unroll
-    for (int q = 0; q < NQ; ++q) {
-        const uint4 v = rq[q * LPR];
-        const unsigned d0 = (unsigned)t - v.x, d1 = (unsigned)t - v.y, d2 = (unsigned)t - v.z, d3 = (unsigned)t - v.w;
-        s0 += d0 >> 31;
-        s1 += d1 >> 31;
-        s2 += d2 >> 31;
-        s3 += d3 >> 31;
-        if (FULL) {
-            mn = s4_umin(mn, s4_umin(s4_umin(d0, d1), s4_umin(d2, d3)));
-            mx = s4_umax(mx, s4_umax(s4_umax(d0, d1), s4_umax(d2, d3)));
-        }
-    }
-    unsigned s = (s0 + s1) + (s2 + s3);
-#pragma unroll
-    for (int o = 1; o < LPR; o <<= 1) {
-        s += __shfl_xor_sync(kFullMask, s, o);
-        if (FULL) {
-            mn = s4_umin(mn, __shfl_xor_sync(kFullMask, mn, o));
-            mx = s4_umax(mx, __shfl_xor_sync(kFullMask, mx, o));
-        }
-    }
-    gt = s;
-    dmin = mn;
-    dmax = mx;
-}
-
-// Threshold search of one row; every lane of the group holds the same copy.
-struct S7Row {
-    int row;       // strip row being resolved, -1: none
-    int t;         // threshold of the next pass
-    int lo, clo;   // count(lo) = clo < k
-    int hi, chi;   // count(hi) = chi >= k
-    int tA, cA;    // previous probe (key spacing estimate)
-    int iter, gallop;
-    float spacing;
-    bool rl, rh, haveA, wantfull;
-};
-
-__device__ __forceinline__ void s7_row_begin(S7Row& S, int row, int t0) {
-    S.row = row;
-    S.t = t0 < 0 ? 0 : (t0 > kKeyInf - 2 ? kKeyInf - 2 : t0);
-    S.lo = -1;
-    S.clo = 0;
-    S.hi = kKeyInf - 1;
-    S.chi = 0x7fffffff;
-    S.tA = S.cA = 0;
-    S.iter = S.gallop = 0;
-    S.rl = S.rh = S.haveA = S.wantfull = false;
-}
-
-// Digest one pass (count c of keys <= S.t; on a full pass `below` = largest key <= t, `above` = smallest
-// key > t or kKeyInf).  Returns true when the k-th and (k+1)-th keys are known.
-__device__ __forceinline__ bool s7_row_step(S7Row& S, int k, int c, bool full, int below, int above, int& vk, int& vk1) {
-    const int t = S.t;
-    if (S.haveA && c != S.cA) {
-        const float sp = fabsf((float)(t - S.tA)) * __fdividef(1.0f, fabsf((float)(c - S.cA)));
-        if (sp >= 1.0f) S.spacing = sp;
-    }
-    S.tA = t;
-    S.cA = c;
-    S.haveA = true;
-    ++S.iter;
-    const int e = k - c;
-    if (e > 0) {
-        S.lo = t; S.clo = c; S.rl = true;
-    } else {
-        S.hi = t; S.chi = c; S.rh = true;
-    }
-    if (e == 0) {
-        if (full) {
-            vk = below;
-            vk1 = above;
-            return true;
-        }
-        S.wantfull = true;  // same threshold again, with the boundary keys
-        return false;
-    }
-    if (full) {
-        if (e < 0 && S.rl && S.lo + 1 == t) {
-            // the count jumps across k between two adjacent integers: ranks k and k + 1 share key t
-            vk = t;
-            vk1 = t;
-            return true;
-        }
-        if (e == 1 && above < kKeyInf) {
-            // `above` IS the k-th key; one more full pass at it yields the (k+1)-th
-            S.t = above;
-            S.wantfull = true;
-            return false;
-        }
-        if (e == -1) {
-            // `below` is the (k+1)-th key
-            if (S.rl && below - 1 <= S.lo) {
-                vk = below;
-                vk1 = below;
-                return true;
-            }
-            S.t = below - 1;
-            S.wantfull = true;
-            return false;
-        }
-    }
-    int nt;
-    if (S.rl && S.rh) {
-        const int width = S.hi - S.lo;
-        if (width <= 1) {
-            nt = S.hi;  // count(hi) >= k > count(hi - 1): a full pass at hi ends the search
-            S.wantfull = true;
-        } else {
-            if (S.iter > 40 || (S.iter % 3) == 0) {
-                nt = S.lo + (width >> 1);
-            } else {
-                const float fr = __fdividef((float)(k - S.clo), (float)(S.chi - S.clo));
-                nt = S.lo + (int)((float)width * fr);
-            }
-            if (nt <= S.lo) nt = S.lo + 1;
-            if (nt >= S.hi) nt = S.hi - 1;
-            if (S.chi - S.clo <= kS7FullW) S.wantfull = true;
-        }
-    } else {
-        float stepf = S.spacing * 1.25f * fabsf((float)e) * (float)(1 << (S.gallop < 20 ? S.gallop : 20));
-        if (stepf < 1.0f) stepf = 1.0f;
-        if (stepf > 1.0e9f) stepf = 1.0e9f;
-        const int step = (int)stepf;
-        ++S.gallop;
-        int64_t n64 = (e > 0) ? (int64_t)t + step : (int64_t)t - step;
-        if (n64 < 0) n64 = 0;
-        if (n64 > kKeyInf - 2) n64 = kKeyInf - 2;
-        if (S.rh && n64 >= S.hi) n64 = S.hi - 1;
-        if (S.rl && n64 <= S.lo) n64 = S.lo + 1;
-        if ((int)n64 == t) {
-            // pinned against the edge of the key domain: the bracket is real on that side
-            if (e > 0) { S.hi = kKeyInf - 1; S.chi = 0x7fffffff; S.rh = true; }
-            else { S.lo = -1; S.clo = 0; S.rl = true; }
-            n64 = S.lo + ((S.hi - S.lo) >> 1);
-            if (n64 <= S.lo) n64 = S.lo + 1;
-        }
-        nt = (int)n64;
-        if (fabsf((float)e) <= (float)kS7FullW) S.wantfull = true;
-    }
-    S.t = nt;
-    return false;
-}
-
 struct Sweep7Args {
     const double* frames;   // [total_frames][BINS]
     const double* wnorm;    // [total_frames] windowed squared norms
@@ -288,16 +141,15 @@ struct Sweep7Args {
 };
 
 template <int MODE, int BINS, int MW, int NT, int CPT>
-__global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 2 : 1))) k_sweep7(Sweep7Args A) {
+__global__ void __launch_bounds__(NT, (S7Cfg<NT, CPT>::MINB)) k_sweep7(Sweep7Args A) {
     using C = S7Cfg<NT, CPT>;
-    constexpr int NC = C::NC, NW = C::NW, LPR = C::LPR, NQ = C::NQ, R = C::R, LCP = C::LCP, WPR = C::WPR;
+    constexpr int NC = C::NC, NW = C::NW, NQ = C::NQ, R = C::R, RPW = C::RPW, LCP = C::LCP, WPR = C::WPR;
     constexpr bool DBS = C::DBS;
     constexpr int KS = (BINS + 3) / 4;  // DMMA k-steps
     constexpr int PPS = R / kS7Per;     // periods per strip
     static_assert(MW <= kS7Pad && MW <= 15, "the zero pad must flush the window");
     ACOSS_DYNSMEM(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int sub = lane & (LPR - 1), glead = lane & ~(LPR - 1);
     const int m = MW;
     const int G = A.gap, BANDW = 2 * A.gap + 6;
     const S7Layout LY = s7_layout<NT, CPT>(BINS, MODE);
@@ -311,16 +163,11 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
     uint32_t* const bits = reinterpret_cast<uint32_t*>(smem_raw + LY.bits);  // [R][wp] CRP words (MODE 2)
     int* const rthr = reinterpret_cast<int*>(smem_raw + LY.rinfo);       // row-relative certainly-in bound
     int* const rkwx = rthr + R;                                          // the row's windowed norm in key units
-    int* const rvk = rthr + 2 * R;
-    int* const rvk1 = rthr + 3 * R;
-    int* const rblo = rthr + 4 * R;
-    int* const rflag = rthr + 5 * R;                                     // 1: flagged (float64 separator in rsepx)
+    int* const rblo = rthr + 2 * R;
+    int* const rflag = rthr + 3 * R;                                     // 1: flagged (float64 separator in rsepx)
     int* const cand = reinterpret_cast<int*>(smem_raw + LY.cand) + warp * (kS4MaxFlag + 1);
     int* const misc = reinterpret_cast<int*>(smem_raw + LY.misc);
-    int* const s_item = misc;        // [0] item, [1] next row of the strip, [2] unsafe rows, [3] guess valid,
-    int* const s_next = misc + 1;    // [4] guess (absolute key), [5] any flagged column
-    int* const s_nunsafe = misc + 2;
-    int* const s_unsafe = misc + 16;
+    int* const s_item = misc;        // [0] item, [5] any flagged column
     uint64_t* const mbar = reinterpret_cast<uint64_t*>(smem_raw + LY.mbar);
 
     if (tid == 0) {
@@ -330,18 +177,33 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
     }
     __syncthreads();
     unsigned par0 = 0, par1 = 0;
-    float spacing_keep = 4096.0f;
+#if ACOSS_S7_STAT
+    int* const s_prof = misc + 16;
+    int tl_ = (int)clock();
+    if (tid < 16) s_prof[tid] = 0;
+#define S7_LAP(k)                                   \
+    if (lane == 0) {                                \
+        const int t_ = (int)clock();                \
+        atomicAdd(&s_prof[k], t_ - tl_);            \
+        tl_ = t_;                                   \
+    }
+#else
+#define S7_LAP(k)
+#endif
+    S4Sel st;  // key spacing around the separator, carried from row to row
+    st.spacing = 1.0f;
+    st.scale = 0.0f;
 
     for (;;) {
         if (tid == 0) {
             *s_item = (int)atomicAdd(A.counter, 1u);
-            misc[3] = 0;
             misc[5] = 0;
         }
         __syncthreads();
         const int it = *s_item;
         __syncthreads();
         if (it >= A.n_items) break;
+        S7_LAP(11);
 
         const uint32_t item = A.items[it];
         int pidx, orient;
@@ -417,10 +279,14 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                     }
                 }
                 const int c = tid + NT * h;
-                csq[c] = (c < Lc) ? cnorm[c] : 0.0;
+                // accumulator seeds of the dot products: the column's squared norm ON TOP OF the fixed-point offset
+                // 1.5 * 2^e, so that every slab entry lies in the binade [2^e, 2^(e+1)) and its bit pattern is a
+                // fixed-point number (stage 2 then adds and subtracts the patterns as 64-bit integers: exact, and
+                // off the FP64 pipe the DMMAs need)
+                csq[c] = ((c < Lc) ? cnorm[c] : 0.0) + OFF;
                 // column sets that hold no column of the song are never written by stage 1: they are the zero pad
                 if (32 * (warp + NW * h) >= Lc)
-                    for (int r = 0; r < (DBS ? 2 : 1) * kS7Per; ++r) slab[r * LCP + c] = 0.0;
+                    for (int r = 0; r < (DBS ? 2 : 1) * kS7Per; ++r) slab[r * LCP + c] = OFF;
                 if (MODE == 2) {
                     // separators of the CRP columns (window index j = c)
                     int v = -1;
@@ -439,17 +305,29 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
         // diagonal column = (row + t) mod NC: by the time it re-enters at column 0 the window has seen 9
         // zeros, so W is back at its offset and nothing needs to be reset.
         int cb[CPT];
-        double W[CPT], ring[CPT][16];
+        const long long OFFB = __double_as_longlong(OFF);
+        long long W[CPT], ring[CPT][16];  // bit patterns: W = offset + window sum, ring = the last 16 slab values
 #pragma unroll
         for (int h = 0; h < CPT; ++h) {
             cb[h] = tid + NT * h;
-            W[h] = OFF;
+            W[h] = OFFB;
 #pragma unroll
-            for (int q = 0; q < 16; ++q) ring[h][q] = 0.0;
+            for (int q = 0; q < 16; ++q) ring[h][q] = OFFB;
         }
         const int nper = (Lr + kS7Per - 1) / kS7Per;
+        const int est_rank = (kk >= 1 && kk < No) ? s4_est_rank(kk, No) : 0;
         __syncthreads();
         const bool any_cflag = (MODE == 2) && misc[5] != 0;
+        double cn[CPT == 1 ? 4 : 1][2];  // one diagonal per thread: the seeds of this warp's 32 columns stay in registers
+        if (CPT == 1) {
+#pragma unroll
+            for (int bi = 0; bi < (CPT == 1 ? 4 : 1); ++bi) {
+                const double2 c2 = *reinterpret_cast<const double2*>(csq + 32 * warp + 8 * bi + 2 * (lane & 3));
+                cn[bi][0] = c2.x;
+                cn[bi][1] = c2.y;
+            }
+        }
+        S7_LAP(0);
 
         // ---- stage 1 of period q: this warp's column sets x 8 rows into the slab
         auto stage1 = [&](int q) {
@@ -480,8 +358,15 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                     const double2* cq = reinterpret_cast<const double2*>(csq + cbase + 2 * (lane & 3));
 #pragma unroll
                     for (int bi = 0; bi < 4; ++bi) {
-                        const double2 c2 = cq[4 * bi];
-                        double c0 = c2.x, c1 = c2.y;
+                        double c0, c1;
+                        if (CPT == 1) {
+                            c0 = cn[CPT == 1 ? bi : 0][0];
+                            c1 = cn[CPT == 1 ? bi : 0][1];
+                        } else {
+                            const double2 c2 = cq[4 * bi];
+                            c0 = c2.x;
+                            c1 = c2.y;
+                        }
 #pragma unroll
                         for (int s = 0; s < KS; ++s) s7_dmma(c0, c1, xa[s], yf[h][bi][s]);
                         double2 cc;
@@ -497,15 +382,18 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
         auto stage2 = [&](auto Hc, int p) {
             constexpr int H = decltype(Hc)::value;
             const int a0 = p * kS7Per;
-            const double* const dslab = slab + (DBS ? (p & 1) * kS7Per * LCP : 0);
+            const long long* const dslab = reinterpret_cast<const long long*>(slab + (DBS ? (p & 1) * kS7Per * LCP : 0));
             int* const sl = strip + (a0 % R) * NC;
+            auto fixb = [](long long w) {  // bits 52..21 of the pattern (s4_fix on the double it encodes)
+                return (int)__funnelshift_r((unsigned)(unsigned long long)w, (unsigned)((unsigned long long)w >> 32), 21);
+            };
 #pragma unroll
             for (int h = 0; h < CPT; ++h) {
                 const int c = cb[h];
                 if (c + kS7Per <= NC) {
-                    const double* dp = dslab + c;
+                    const long long* dp = dslab + c;
                     int* sp = sl + c;
-                    double v[kS7Per];
+                    long long v[kS7Per];
 #pragma unroll
                     for (int r = 0; r < kS7Per; ++r) v[r] = dp[r * (LCP + 1)];
                     if (a0 >= MW - 1 && c >= MW - 1 && c + kS7Per <= Lc) {
@@ -514,7 +402,7 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                         for (int r = 0; r < kS7Per; ++r) {
                             W[h] += v[r] - ring[h][(8 * H + r - MW) & 15];
                             ring[h][8 * H + r] = v[r];
-                            sp[r * (NC + 1)] = s4_fix(W[h]);
+                            sp[r * (NC + 1)] = fixb(W[h]);
                         }
                     } else {
                         // no wrap, but some keys are invalid (first rows / first columns / the zero pad)
@@ -523,7 +411,7 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                             W[h] += v[r] - ring[h][(8 * H + r - MW) & 15];
                             ring[h][8 * H + r] = v[r];
                             const bool ok = (unsigned)(c + r - (MW - 1)) < (unsigned)No && a0 + r >= MW - 1;
-                            sp[r * (NC + 1)] = ok ? s4_fix(W[h]) : kKeyInf;
+                            sp[r * (NC + 1)] = ok ? fixb(W[h]) : kKeyInf;
                         }
                     }
                 } else {
@@ -532,11 +420,11 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                     for (int r = 0; r < kS7Per; ++r) {
                         int col = c + r;
                         if (col >= NC) col -= NC;
-                        const double v = dslab[r * LCP + col];
+                        const long long v = dslab[r * LCP + col];
                         W[h] += v - ring[h][(8 * H + r - MW) & 15];
                         ring[h][8 * H + r] = v;
                         const bool ok = (unsigned)(col - (MW - 1)) < (unsigned)No && a0 + r >= MW - 1;
-                        sl[r * NC + col] = ok ? s4_fix(W[h]) : kKeyInf;
+                        sl[r * NC + col] = ok ? fixb(W[h]) : kKeyInf;
                     }
                 }
                 cb[h] = (c + kS7Per >= NC) ? c + kS7Per - NC : c + kS7Per;
@@ -545,21 +433,38 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
 
         if (DBS) {
             stage1(0);
+            S7_LAP(1);
             __syncthreads();
+            S7_LAP(3);
         }
         bool pre_done = false;  // !DBS: stage 1 of the coming period already ran (behind the selection)
+        bool pre2 = false;      // DBS: stage 1 of the period after the coming one ran behind the selection too
         for (int p = 0; p < nper; ++p) {
             if (!DBS) {
                 if (!pre_done) stage1(p);
                 pre_done = false;
+                S7_LAP(1);
                 __syncthreads();  // the slab of period p is complete
+                S7_LAP(3);
+            }
+            const bool end_strip = ((p + 1) % PPS == 0) || (p + 1 == nper);
+            // Half of the warps of every scheduler (warps 4..7, 12..15, ...) run the next period's dot products BEFORE
+            // their diagonal walk, the other half after it: the FP64 tensor pipe and the integer / LSU pipes are then
+            // busy at the same time instead of one after the other.
+            const bool s1_first = DBS && !end_strip && ((warp >> 2) & 1) && !pre2;
+            if (s1_first) {
+                stage1(p + 1);
+                S7_LAP(1);
             }
             if (p & 1) stage2(std::integral_constant<int, 1>(), p);
             else stage2(std::integral_constant<int, 0>(), p);
-            const bool end_strip = ((p + 1) % PPS == 0) || (p + 1 == nper);
+            S7_LAP(2);
             if (!end_strip) {
-                if (DBS) stage1(p + 1);
+                if (DBS && !s1_first && !pre2) stage1(p + 1);
+                pre2 = false;
+                S7_LAP(1);
                 __syncthreads();  // keys of period p, (DBS) slab of period p + 1
+                S7_LAP(3);
                 continue;
             }
 
@@ -569,10 +474,7 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
             const int s_first = imax(0, (m - 1) - a_base);                // first strip row that is a window
             const int s_last = imin(R - 1, Lr - 1 - a_base);
             const int nsel = s_last - s_first + 1;
-            if (tid == 0) {
-                *s_next = 0;
-                *s_nunsafe = 0;
-            }
+            if (tid == 0) misc[6] = 0;
             if (tid < R) {
                 const int a = a_base + tid;
                 rkwx[tid] = (a < Lr) ? s4_fix(rwn[a] + BIGE) : 0;
@@ -580,113 +482,97 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                 rthr[tid] = (kk <= 0) ? -1 : ((A.flags & (1u << 30)) ? (1 << 30) : (kKeyInf - 1));
             }
             __syncthreads();  // the keys of the strip are complete
+            S7_LAP(4);
 
-            if (do_select && nsel > 0) {
-                S7Row S;
-                S.row = -1;
-                S.spacing = spacing_keep;
-                bool exhausted = false;
-#if ACOSS_S7_STAT
-                unsigned n_cnt = 0, n_full = 0, n_rows = 0;
-#endif
-                for (;;) {
-                    // idle groups fetch the next row of the strip
-                    const bool need = S.row < 0 && !exhausted;
-                    int r = 0;
-                    if (need && sub == 0) r = atomicAdd(s_next, 1);
-                    r = __shfl_sync(kFullMask, r, glead);
-                    if (need) {
-                        if (r < nsel) {
-                            const int srow = s_first + r;
-                            const volatile int* vm = misc;
-                            const int t0 = vm[3] ? (vm[4] - rkwx[srow]) : (1 << 30);
-                            s7_row_begin(S, srow, t0);
-                        } else {
-                            exhausted = true;
-                        }
-                    }
-                    if (__all_sync(kFullMask, S.row < 0)) break;
-                    const int srow = S.row < 0 ? s_first : S.row;
-                    const uint4* rq = reinterpret_cast<const uint4*>(strip + srow * NC) + sub;
-                    const bool full = __any_sync(kFullMask, S.row >= 0 && S.wantfull);
-                    unsigned gt, dmin, dmax;
-                    if (full) s7_pass<LPR, NQ, true>(rq, S.t, gt, dmin, dmax);
-                    else s7_pass<LPR, NQ, false>(rq, S.t, gt, dmin, dmax);
-#if ACOSS_S7_STAT
-                    if (S.row >= 0) { if (full) ++n_full; else ++n_cnt; }
-#endif
-                    if (S.row >= 0) {
-                        const int c = NC - (int)gt;
-                        const int below = S.t - (int)dmin;
-                        const int above = (dmax >= 0x80000000u) ? (int)((unsigned)S.t - dmax) : kKeyInf;
-                        int vk, vk1;
-                        if (s7_row_step(S, kk, c, full, below, above, vk, vk1)) {
-                            if (sub == 0) {
-                                const int gapk = vk1 - vk;
-                                if (gapk >= 2 * G) {
-                                    const int thr = vk + (gapk >> 1);
-                                    rthr[S.row] = thr;
-                                    volatile int* vm = misc;
-                                    vm[4] = thr + rkwx[S.row];
-                                    vm[3] = 1;
-                                } else {
-                                    rvk[S.row] = vk;
-                                    rvk1[S.row] = vk1;
-                                    s_unsafe[atomicAdd(s_nunsafe, 1)] = S.row;
-                                }
+            // ---- this warp's chain of RPW consecutive rows: separator, then (MODE 2) the row's CRP words
+            if (nsel > 0 && (do_select || MODE == 2)) {
+                bool have_prev = false;
+                int prev_abs = 0;
+#pragma unroll 1
+                for (int q = 0; q < RPW; ++q) {
+                    const int srow = warp * RPW + q;
+                    if (srow < s_first || srow > s_last) continue;
+                    const int* krow = strip + srow * NC;
+                    const int kwx = rkwx[srow];
+                    int thr = rthr[srow];
+                    if (do_select) {
+                        const uint4* row4 = reinterpret_cast<const uint4*>(krow);
+                        S4Keys<NQ> keys;
+                        keys.load_strided(krow, lane);
+                        int t0 = prev_abs - kwx;
+                        bool have_g = have_prev;
+                        if (!have_prev) {
+                            const int ge = s4_estimate(keys, est_rank, lane);
+                            if (ge < kKeyInf - 1) {
+                                t0 = ge;
+                                have_g = true;
                             }
-#if ACOSS_S7_STAT
-                            ++n_rows;
-#endif
-                            S.row = -1;
                         }
+                        int vk, vk1;
+                        s4_select(keys, kk, No, t0, have_g, st, lane, vk, vk1);
+                        const int gapk = vk1 - vk;
+                        if (gapk >= 2 * G) {
+                            thr = vk + (gapk >> 1);
+                            prev_abs = thr + kwx;
+                        } else {
+                            // the two keys are closer than 2G: decide in float64
+                            const int irow = a_base + srow - (m - 1);
+                            double sx = 0.0;
+                            int ncand = 0;
+                            unsigned in_mask = 0;
+                            const bool ok = s4_resolve_unsafe(row4, NQ, kk, vk, vk1, pp, irow, m, lane, cand, cand + kS4MaxFlag,
+                                                              sx, ncand, in_mask);
+                            if (ok) {
+                                thr = vk - 3 - 1;
+                                if (lane == 0) {
+                                    misc[6] = 1;
+                                    rflag[srow] = 1;
+                                    rblo[srow] = vk - 3;
+                                    rsepx[srow] = sx;
+                                }
+                            } else {
+                                thr = vk;  // tie cluster: the reference's own choice is undefined here
+                            }
+                            prev_abs = vk + kwx;
+#if ACOSS_S7_STAT
+                            if (lane == 0) atomicAdd(&g_s7_stats[1], 1ull);
+#endif
+                        }
+                        if (lane == 0) rthr[srow] = thr;
+                        have_prev = true;
+#if ACOSS_S7_STAT
+                        if (lane == 0) atomicAdd(&g_s7_stats[0], 1ull);
+#endif
+                    }
+                    if (MODE == 2) {
+                        // CRP words of the row: lane = column within the word (window j <-> frame column j + m - 1)
+                        unsigned mine = 0;
+#pragma unroll
+                        for (int w = 0; w < WPR; ++w) {
+                            if (w < wp) {
+                                const int j = 32 * w + lane;
+                                const int key = (j + (MW - 1) < NC) ? krow[j + (MW - 1)] : kKeyInf;
+                                const unsigned bw = __ballot_sync(kFullMask, key <= imin(thr, csk_s[j] - kwx));
+                                if (lane == w) mine = bw;
+                            }
+                        }
+                        if (lane < wp) bits[srow * wp + lane] = mine;
                     }
                 }
-                spacing_keep = S.spacing;
-#if ACOSS_S7_STAT
-                if (sub == 0) {
-                    atomicAdd(&g_s7_stats[0], (unsigned long long)n_rows);
-                    atomicAdd(&g_s7_stats[1], (unsigned long long)n_cnt);
-                    atomicAdd(&g_s7_stats[2], (unsigned long long)n_full);
-                }
-#endif
             }
+            S7_LAP(5);
             // early finishers start the next period's dot products while the others still select
-            if (p + 1 < nper) {
+            if (p + 1 < nper && !pre2) {
                 stage1(p + 1);
                 pre_done = true;
-            }
-            __syncthreads();  // every row of the strip has its k-th / (k+1)-th keys
-
-            // ---- unsafe rows: the two keys are closer than 2G, decide in float64 (one warp per row)
-            const int nunsafe = *s_nunsafe;
-            if (nunsafe > 0) {
-                for (int u = warp; u < nunsafe; u += NW) {
-                    const int srow = s_unsafe[u];
-                    const int vk = rvk[srow], vk1 = rvk1[srow];
-                    const int irow = a_base + srow - (m - 1);
-                    double sx = 0.0;
-                    int ncand = 0;
-                    unsigned in_mask = 0;
-                    const bool ok = s4_resolve_unsafe(reinterpret_cast<const uint4*>(strip + srow * NC), NC / 128, kk, vk, vk1,
-                                                      pp, irow, m, lane, cand, cand + kS4MaxFlag, sx, ncand, in_mask);
-                    if (lane == 0) {
-                        if (ok) {
-                            rflag[srow] = 1;
-                            rblo[srow] = vk - 3;
-                            rsepx[srow] = sx;
-                            rthr[srow] = vk - 3 - 1;
-                        } else {
-                            rthr[srow] = vk;  // tie cluster: the reference's own choice is undefined here
-                        }
-#if ACOSS_S7_STAT
-                        atomicAdd(&g_s7_stats[3], 1ull);
-#endif
-                    }
-                    __syncwarp();
+                if (DBS && p + 2 < nper && ((p + 2) % PPS != 0)) {
+                    stage1(p + 2);  // both slabs are free behind the strip's last diagonal walk
+                    pre2 = true;
                 }
-                __syncthreads();
             }
+            S7_LAP(1);
+            __syncthreads();  // every row of the strip has its separator (MODE 2: and its CRP words)
+            S7_LAP(6);
 
             if (MODE == 0) {
                 if (tid >= s_first && tid <= s_last) {
@@ -700,30 +586,11 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                         A.sepk[rsep_off + irow] = (thr < 0) ? 0 : ((thr >= kKeyInf - 1) ? kKeyInf - 1 : thr + kwx);
                     }
                 }
+                S7_LAP(7);
             } else if (nsel > 0) {
-                // ---- CRP words: thread = CRP column (window j = frame column j + m - 1), one ballot per row
-#pragma unroll
-                for (int h = 0; h < CPT; ++h) {
-                    const int j = tid + NT * h;
-                    const int wi = j >> 5;
-                    if (wi < wp) {  // warp-uniform
-                        const int cs = csk_s[j];
-                        const int* kp = strip + s_first * NC + j + (MW - 1);
-                        const bool in_strip = j + (MW - 1) < NC;
-                        for (int s = s_first; s <= s_last; ++s, kp += NC) {
-                            const int key = in_strip ? *kp : kKeyInf;
-                            const int bound = imin(rthr[s], cs - rkwx[s]);
-                            const unsigned w = __ballot_sync(kFullMask, key <= bound);
-                            if (lane == 0) bits[s * wp + wi] = w;
-                        }
-                    }
-                }
-                bool fix = false;
-                if (any_cflag) fix = true;
-                else
-                    for (int s = s_first; s <= s_last; ++s) fix = fix || rflag[s] != 0;  // smem broadcast, uniform
+                S7_LAP(7);
+                const bool fix = any_cflag || misc[6] != 0;  // a flagged column of the item or a flagged row of the strip
                 if (fix) {
-                    __syncthreads();
                     // cells of flagged rows / flagged columns: recompute the decision with the float64 bands
                     for (int pass = 0; pass < 2; ++pass) {
 #pragma unroll
@@ -776,9 +643,8 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                         }
                         __syncthreads();
                     }
-                } else {
-                    __syncthreads();
                 }
+                S7_LAP(8);
                 // ---- the strip's rows are one contiguous run of words in the packed CRP
                 {
                     uint32_t* dst = A.crp + pwp->crp_off + (int64_t)(a_base + s_first - (m - 1)) * wp;
@@ -786,9 +652,21 @@ __global__ void __launch_bounds__(NT, (NT * CPT <= 128 ? 4 : (NT * CPT <= 256 ? 
                     const int nwords = nsel * wp;
                     for (int e = tid; e < nwords; e += NT) dst[e] = src[e];
                 }
+                S7_LAP(9);
             }
             __syncthreads();  // the strip, the row records and the CRP words are free again
+            S7_LAP(10);
+#if ACOSS_S7_STAT
+            if (tid == 0) atomicAdd(&g_s7_stats[2], 1ull);
+#endif
         }
+#if ACOSS_S7_STAT
+        if (tid < 12) {
+            atomicAdd(&g_s7_stats[4 + tid], (unsigned long long)(unsigned)s_prof[tid]);
+            s_prof[tid] = 0;
+        }
+        if (tid == 0) atomicAdd(&g_s7_stats[3], 1ull);
+#endif
     }
 }
 

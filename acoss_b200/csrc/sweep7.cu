@@ -2,6 +2,7 @@
 // api.cu calls.  A separate file so that the library builds in parallel and a change to this kernel does not
 // recompile the rest.
 #include <algorithm>
+#include <cstdlib>
 
 #include "ctx.h"
 #include "kernels_sweep7.cuh"
@@ -47,7 +48,9 @@ int launch_bucket(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket
     switch (bucket) {
         case 0: return launch_one<MODE, BINS, 128, 1>(c, d_items, n_items, d_counter, flags, stream);
         case 1: return launch_one<MODE, BINS, 256, 1>(c, d_items, n_items, d_counter, flags, stream);
-        case 2: return launch_one<MODE, BINS, 512, 1>(c, d_items, n_items, d_counter, flags, stream);
+        case 2:
+            if (c->opt_debug_flags & (1u << 20)) return launch_one<MODE, BINS, 512, 1>(c, d_items, n_items, d_counter, flags, stream);
+            return launch_one<MODE, BINS, 256, 2>(c, d_items, n_items, d_counter, flags, stream);
         case 3: return launch_one<MODE, BINS, 384, 2>(c, d_items, n_items, d_counter, flags, stream);
         case 4: return launch_one<MODE, BINS, 512, 2>(c, d_items, n_items, d_counter, flags, stream);
     }
@@ -70,27 +73,32 @@ size_t acoss_sweep7_smem(int bucket, int bins, int mode) {
     switch (bucket) {
         case 0: return (size_t)s7_layout<128, 1>(bins, mode).total;
         case 1: return (size_t)s7_layout<256, 1>(bins, mode).total;
-        case 2: return (size_t)s7_layout<512, 1>(bins, mode).total;
+        case 2: return std::max((size_t)s7_layout<512, 1>(bins, mode).total, (size_t)s7_layout<256, 2>(bins, mode).total);
         case 3: return (size_t)s7_layout<384, 2>(bins, mode).total;
         default: return (size_t)s7_layout<512, 2>(bins, mode).total;
     }
 }
 
-int acoss_sweep7_stats(acoss_ctx* c, unsigned long long out[8], int reset) {
+int acoss_sweep7_stats(acoss_ctx* c, unsigned long long out[16], int reset) {
 #if ACOSS_S7_STAT
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
-    unsigned long long h[8];
+    unsigned long long h[16];
     CU(cudaMemcpyFromSymbol(h, g_s7_stats, sizeof(h)));
-    for (int i = 0; i < 8; ++i) out[i] = h[i];
+    for (int i = 0; i < 16; ++i) out[i] = h[i];
+    unsigned long long h4[8];
+    CU(cudaMemcpyFromSymbol(h4, g_s4_sel_stats, sizeof(h4)));
+    if (getenv("ACOSS_S4_SEL_STATS"))  // selection statistics replace the phase cycles [4..11]
+        for (int i = 0; i < 8; ++i) out[4 + i] = h4[i];
     if (reset) {
         memset(h, 0, sizeof(h));
         CU(cudaMemcpyToSymbol(g_s7_stats, h, sizeof(h)));
+        CU(cudaMemcpyToSymbol(g_s4_sel_stats, h, sizeof(h4)));
     }
 #else
     (void)c;
     (void)reset;
-    for (int i = 0; i < 8; ++i) out[i] = 0;
+    for (int i = 0; i < 16; ++i) out[i] = 0;
 #endif
     return ACOSS_OK;
 }

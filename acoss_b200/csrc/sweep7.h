@@ -17,4 +17,4 @@ inline int sweep7_bucket_for(int Lc) {  // -1: the column song does not fit
 int acoss_launch_sweep7(acoss_ctx* c, int mode, int bins, const uint32_t* d_items, int n_items, int bucket, unsigned int* d_counter,
                         uint32_t flags);
 size_t acoss_sweep7_smem(int bucket, int bins, int mode);
-int acoss_sweep7_stats(acoss_ctx* c, unsigned long long out[8], int reset);
+int acoss_sweep7_stats(acoss_ctx* c, unsigned long long out[16], int reset);

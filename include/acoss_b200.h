@@ -195,10 +195,10 @@ int acoss_set_option(acoss_ctx* ctx, const char* name, int64_t value);
 /* Profiling aid (not part of the drop-in surface): cycle counters of the gen-6 sweep, see api.cu. */
 int acoss_debug_sweep6_cycles(acoss_ctx* ctx, uint64_t out[8], int reset);
 
-/* Profiling aid: selection statistics of the gen-7 sweep, summed over all launches: [0] rows resolved,
- * [1] counting passes, [2] passes that also tracked the boundary keys, [3] rows decided in float64.
- * All zero unless the library was built with -DACOSS_S7_STATS. */
-int acoss_debug_sweep7_stats(acoss_ctx* ctx, uint64_t out[8], int reset);
+/* Profiling aid: counters of the gen-7 sweep, summed over all launches: [0] rows resolved, [1] rows decided in
+ * float64, [2] strips, [3] items, [4..15] cycles per phase (kernels_sweep7.cuh).  All zero unless the library was
+ * built with -DACOSS_S7_STATS. */
+int acoss_debug_sweep7_stats(acoss_ctx* ctx, uint64_t out[16], int reset);
 
 /* Counters for bench.py: kernels launched by this context since creation / last reset. */
 int64_t acoss_kernel_launches(acoss_ctx* ctx);

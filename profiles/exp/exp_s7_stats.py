@@ -17,13 +17,17 @@ songs, _ = synth.make_song_set("whatisacover", seed=10000, n_songs=10000)
 ctx = _native.Context(0)
 ctx.upload_songs(songs)
 ctx.set_option("sweep_gen", gen)
-out = (ctypes.c_uint64 * 8)()
+out = (ctypes.c_uint64 * 16)()
 for step in range(3):
     pairs = bench.step_pairs(10000, n_pairs, step, 0, 1)
     ctx.lib.acoss_debug_sweep7_stats(ctx._h, out, 1)
     ctx.serra09_pairs(pairs)
     ctx.lib.acoss_debug_sweep7_stats(ctx._h, out, 0)
-    rows, cnt, full, unsafe = [int(out[i]) for i in range(4)]
+    rows, unsafe, strips, cyc, s2, sel, s1, wait = [int(out[i]) for i in range(8)]
     ms = ctx.last_stage_ms()
-    print("step %d: %s  rows %d count passes/row %.2f full passes/row %.2f unsafe rows %d" % (
-        step, {k: round(v, 2) for k, v in ms.items()}, rows, cnt / max(rows, 1), full / max(rows, 1), unsafe), flush=True)
+    tot = max(cyc, 1)
+    print("step %d: %s  rows %d unsafe %d strips %d; warp cycles: stage2 %.1f%% selection %.1f%% stage1 %.1f%% barrier-wait %.1f%% "
+          "rest %.1f%%; per strip and warp: total %.0f sel %.0f s1 %.0f s2 %.0f" % (
+              step, {k: round(v, 2) for k, v in ms.items()}, rows, unsafe, strips, 100 * s2 / tot, 100 * sel / tot, 100 * s1 / tot,
+              100 * wait / tot, 100 * (tot - s2 - sel - s1 - wait) / tot, cyc / max(strips, 1) / 12, sel / max(strips, 1) / 12,
+              s1 / max(strips, 1) / 12, s2 / max(strips, 1) / 12), flush=True)
