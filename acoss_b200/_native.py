@@ -172,6 +172,20 @@ class Context:
     def upload_songs(self, songs):
         self.upload(*pack_songs(songs))
 
+    def upload_device(self, frames_ptr, dtype, bins, offsets, lengths, gchroma_ptr=None):
+        """Same as upload() for an arena that already lives in DEVICE memory (addresses as integers, e.g. a torch
+        tensor's data_ptr()): frames [total_frames][bins] of float32 / float64, gchroma [n_songs][bins] float64 or
+        None.  The copy is device-to-device; the producer of the buffers must have finished."""
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+        self.lengths = lengths.copy()
+        self.bins = int(bins)
+        dt = F32 if np.dtype(dtype) == np.float32 else F64
+        rc = self.lib.acoss_upload_songs(self._h, ctypes.c_void_p(int(frames_ptr)), dt, _ptr(offsets, _c_i64p),
+                                         _ptr(lengths, _c_i32p), len(lengths), self.bins,
+                                         ctypes.cast(ctypes.c_void_p(int(gchroma_ptr)), _c_f64p) if gchroma_ptr else None)
+        self._check(rc, "acoss_upload_songs")
+
     # ------------------------------------------------------------------ scoring
     def serra09_pairs(self, pairs, m=9, kappa=0.095, flags=0, want_crp=False, want_sw=False):
         """pairs: (P, 2) int array.  Returns dict with qmax_raw, dmax_raw (float32), oti (int32),

@@ -859,10 +859,10 @@ int acoss_upload_songs(acoss_ctx* c, const void* frames, int dtype, const int64_
     CU(c->norms.reserve(std::max<size_t>((size_t)total, 1) * sizeof(double)));
     CU(c->offs.reserve((size_t)n_songs * sizeof(int64_t)));
     if (dtype == ACOSS_F64) {
-        CU(cudaMemcpyAsync(c->frames.p, frames, n_el * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->frames.p, frames, n_el * sizeof(double), cudaMemcpyDefault, c->stream));  // host or device source
     } else {
         CU(c->dense_in.reserve(std::max<size_t>(n_el, 1) * sizeof(float)));
-        CU(cudaMemcpyAsync(c->dense_in.p, frames, n_el * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->dense_in.p, frames, n_el * sizeof(float), cudaMemcpyDefault, c->stream));
         if (n_el) {
             auto kfn = k_f32_to_f64;
             ACOSS_LAUNCH(kfn, (n_el + 255) / 256, 256, 0, c->stream, c->dense_in.as<float>(), c->frames.as<double>(),
@@ -883,7 +883,7 @@ int acoss_upload_songs(acoss_ctx* c, const void* frames, int dtype, const int64_
     c->has_gchroma = gchroma != nullptr;
     CU(c->gchroma.reserve((size_t)n_songs * bins * sizeof(double)));
     if (gchroma)
-        CU(cudaMemcpyAsync(c->gchroma.p, gchroma, (size_t)n_songs * bins * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(c->gchroma.p, gchroma, (size_t)n_songs * bins * sizeof(double), cudaMemcpyDefault, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     return ACOSS_OK;

@@ -1,14 +1,21 @@
-"""Multi-GPU plumbing for the all-pairs run: one process per GPU (torchrun), songs shared once,
-the upper-triangular pair matrix cut into T x T song tiles that are dealt to ranks by estimated
-cost, score tiles gathered back on rank 0.  There is no per-pair communication and no
-data-path collective: pairs are independent units.
+"""Multi-GPU plumbing for the all-pairs run: one process per GPU (torchrun).
 
-torch.distributed is used only as the transport (NCCL over NVLink/NVSwitch on the GPU box, gloo
-in the CPU tests); the compute goes through the C ABI on each rank's own device.
+  * SONGS are all-gathered once: every rank loads / packs the features of its contiguous share of the songs,
+    copies that shard to its device, and one all_gather over NCCL (NVLink / NVSwitch) gives every rank the whole
+    arena in device memory; acoss_upload_songs takes the device pointer (device-to-device, no host bounce).
+  * PAIRS: the upper-triangular pair matrix is cut into T x T song tiles that are dealt to ranks by estimated
+    cost (sum of M * N), longest-processing-time greedy.  Pairs are independent: no data-path collective.
+  * SCORES come back as float32 tiles: one gather of [n_types, n_pairs_of_rank] float32 to rank 0, which knows
+    every rank's tile list and drops the tiles into the N x N matrices by slicing.
+
+torch.distributed is used only as the transport (NCCL on the GPU box, gloo in the CPU tests); the compute goes
+through the C ABI on each rank's own device (CoverAlgorithm.py:138-184 is the single-process
+original).
 """
 from __future__ import annotations
 
 import os
+import time
 
 import numpy as np
 
@@ -28,48 +35,112 @@ def init_distributed(backend=None):
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29511")
-        dist.init_process_group(backend=backend or ("nccl" if use_cuda else "gloo"), rank=rank, world_size=world)
+        kw = {}
+        if use_cuda and (backend in (None, "nccl")):
+            kw["device_id"] = torch.device("cuda", local)
+        dist.init_process_group(backend=backend or ("nccl" if use_cuda else "gloo"), rank=rank, world_size=world, **kw)
     device = torch.device("cuda", local) if use_cuda else torch.device("cpu")
     return rank, world, local, device
 
 
-def _bcast_array(arr, meta_src, src, device):
-    """Broadcast a numpy array from `src` (other ranks pass arr=None)."""
-    import torch
+def _is_dist():
     import torch.distributed as dist
-    rank = dist.get_rank()
-    meta = [None]
-    if rank == src:
-        meta = [(arr.shape, str(arr.dtype))]
-    dist.broadcast_object_list(meta, src=src)
-    shape, dtype = meta[0]
-    if rank == src:
-        t = torch.from_numpy(np.ascontiguousarray(arr)).to(device)
-    else:
-        t = torch.empty(shape, dtype=getattr(torch, dtype), device=device)
-    dist.broadcast(t, src=src)
-    return t.cpu().numpy()
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 
 
-def broadcast_songs(packed, src=0, device=None):
-    """Share the packed song arena (frames, offsets, lengths, gchroma) from rank `src` with every
-    rank -- the one feature collective of a run.  Single-process: returns `packed` unchanged."""
+def _default_device():
     import torch
     import torch.distributed as dist
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
-        return packed
+    return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+
+
+def _allgather(t):
+    """all_gather of equal-shaped tensors -> [world, *t.shape] (flat buffers: gloo and NCCL agree on those)."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size()
+    flat = t.contiguous().view(-1)
+    out = torch.empty(world * flat.numel(), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out, flat)
+    return out.view((world,) + tuple(t.shape))
+
+
+def song_shares(n_songs, world):
+    """Contiguous song-id ranges [s0, s1) per rank (the shard a rank loads and contributes to the all-gather)."""
+    cuts = np.linspace(0, n_songs, world + 1).astype(np.int64)
+    return [(int(cuts[r]), int(cuts[r + 1])) for r in range(world)]
+
+
+# ---------------------------------------------------------------------------- songs: all-gather
+class SharedArena:
+    """The whole song arena on this rank's device after the all-gather.  frames: torch tensor [total_frames, bins]
+    (float32 / float64) on `device`; gchroma: [n_songs, bins] float64 tensor or None; offsets / lengths: host arrays."""
+
+    def __init__(self, frames, gchroma, offsets, lengths, seconds):
+        self.frames, self.gchroma, self.offsets, self.lengths, self.seconds = frames, gchroma, offsets, lengths, seconds
+
+    def upload_into(self, ctx):
+        import torch
+        if self.frames.is_cuda:
+            torch.cuda.current_stream(self.frames.device).synchronize()   # the collective has finished
+            ctx.upload_device(self.frames.data_ptr(), np.float32 if self.frames.dtype == torch.float32 else np.float64,
+                              self.frames.shape[1], self.offsets, self.lengths,
+                              None if self.gchroma is None else self.gchroma.data_ptr())
+        else:  # gloo / CPU tests: the same call with host pointers
+            ctx.upload(self.frames.numpy(), self.offsets, self.lengths, None if self.gchroma is None else self.gchroma.numpy())
+
+
+def allgather_songs(shard, device=None):
+    """shard = (frames [n_frames_local, bins] host array (pinned or not), lengths int32 [n_local], gchroma float64
+    [n_local, bins] or None) of THIS rank's songs (ranks hold consecutive song-id ranges, rank order = song order).
+    Returns a SharedArena.  One host->device copy of the local shard, one all_gather of lengths, one of frames, one of
+    gchroma; nothing goes back to the host."""
+    import torch
+    import torch.distributed as dist
+    t0 = time.perf_counter()
+    frames, lengths, g = shard
+    single = not _is_dist()
     if device is None:
-        device = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
-    rank = dist.get_rank()
-    has_g = [packed[3] is not None] if rank == src else [None]
-    dist.broadcast_object_list(has_g, src=src)
-    out = []
-    for k in range(4):
-        if k == 3 and not has_g[0]:
-            out.append(None)
-            continue
-        out.append(_bcast_array(packed[k] if rank == src else None, None, src, device))
-    return tuple(out)
+        device = _default_device() if not single else (torch.device("cuda", torch.cuda.current_device())
+                                                       if torch.cuda.is_available() else torch.device("cpu"))
+    lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+    n_local = int(lengths.size)
+    nf_local = int(lengths.astype(np.int64).sum())
+    bins = int(frames.shape[1])
+    tf = torch.from_numpy(np.ascontiguousarray(frames[:max(nf_local, 0)])).to(device, non_blocking=True)
+    tg = None if g is None else torch.from_numpy(np.ascontiguousarray(g, dtype=np.float64)).to(device, non_blocking=True)
+    if single:
+        offsets = np.zeros(n_local, np.int64)
+        if n_local > 1:
+            offsets[1:] = np.cumsum(lengths[:-1].astype(np.int64))
+        return SharedArena(tf, tg, offsets, lengths, time.perf_counter() - t0)
+    world = dist.get_world_size()
+    meta = torch.tensor([n_local, nf_local, 0 if g is None else 1], dtype=torch.int64, device=device)
+    metas = _allgather(meta).cpu().numpy()
+    ns, nf, has_g = metas[:, 0], metas[:, 1], bool(metas[:, 2].min())
+    max_s, max_f = int(ns.max()), int(nf.max())
+    # lengths
+    tl = torch.zeros(max_s, dtype=torch.int32, device=device)
+    tl[:n_local] = torch.from_numpy(lengths).to(device)
+    all_l = _allgather(tl).cpu().numpy()
+    lengths_all = np.concatenate([all_l[r, :ns[r]] for r in range(world)]).astype(np.int32)
+    # frames: equal-sized (padded) shards, compacted on the device
+    pad = torch.zeros((max_f, bins), dtype=tf.dtype, device=device)
+    pad[:nf_local] = tf
+    all_f = _allgather(pad)
+    arena = torch.cat([all_f[r, :nf[r]] for r in range(world)], dim=0).contiguous()
+    garena = None
+    if has_g:
+        pg = torch.zeros((max_s, bins), dtype=torch.float64, device=device)
+        pg[:n_local] = tg
+        all_g = _allgather(pg)
+        garena = torch.cat([all_g[r, :ns[r]] for r in range(world)], dim=0).contiguous()
+    offsets = np.zeros(lengths_all.size, np.int64)
+    if lengths_all.size > 1:
+        offsets[1:] = np.cumsum(lengths_all[:-1].astype(np.int64))
+    if arena.is_cuda:
+        torch.cuda.synchronize(device)
+    return SharedArena(arena, garena, offsets, lengths_all, time.perf_counter() - t0)
 
 
 # ---------------------------------------------------------------------------- tiling
@@ -107,7 +178,8 @@ def tile_costs(lengths, T, tiles, m=9):
 
 def assign_tiles(costs, world):
     """Longest-processing-time greedy: tiles by decreasing cost to the least-loaded rank.
-    Returns a list of tile-index arrays, one per rank (deterministic on every rank)."""
+    Returns (list of tile-index arrays, one per rank, each in ascending tile order; per-rank load).  Deterministic
+    on every rank."""
     order = np.argsort(-costs, kind="stable")
     load = np.zeros(world)
     owner = np.zeros(len(costs), dtype=np.int64)
@@ -118,68 +190,118 @@ def assign_tiles(costs, world):
     return [np.nonzero(owner == r)[0] for r in range(world)], load
 
 
-def shard_pairs(n_songs, lengths, world, rank, T=128, m=9):
+def shard_tiles(n_songs, lengths, world, T=128, m=9, tiles=None):
+    """(tiles, per-rank tile-index arrays, per-rank estimated load) of an all-pairs run."""
+    tiles = tile_list(n_songs, T) if tiles is None else tiles
+    shares, load = assign_tiles(tile_costs(lengths, T, tiles, m), world)
+    return tiles, shares, load
+
+
+def shard_pairs(n_songs, lengths, world, rank, T=128, m=9, tiles=None):
     """This rank's share of the all-pairs list: concatenated pairs of its tiles."""
-    tiles = tile_list(n_songs, T)
-    shares, _ = assign_tiles(tile_costs(lengths, T, tiles, m), world)
+    tiles, shares, _ = shard_tiles(n_songs, lengths, world, T, m, tiles)
     mine = [tile_pairs(n_songs, T, tiles[t]) for t in shares[rank]]
     if not mine:
         return np.zeros((0, 2), np.int32)
     return np.concatenate(mine, axis=0)
 
 
-def gather_scores(idxs, scores, dst=0, device=None):
-    """Gather per-rank (idxs (P,2) int32, scores {key: float64 (P,)}) on rank `dst`.
-    Returns (idxs_all, scores_all) on dst, (None, None) elsewhere.  Single-process: identity."""
+def tile_pair_count(n_songs, T, tile):
+    a, b = tile
+    ni = min((a + 1) * T, n_songs) - a * T
+    nj = min((b + 1) * T, n_songs) - b * T
+    return ni * nj if a != b else ni * (ni - 1) // 2
+
+
+# ---------------------------------------------------------------------------- scores: float32 tiles to rank 0
+def gather_score_tiles(local, dst=0, device=None):
+    """local: float32 array [n_types, n_local_pairs] of this rank (pairs in the order of its tile list).
+    Returns on `dst` a list of per-rank [n_types, n_pairs_of_rank] arrays, None elsewhere.  Single process: [local]."""
     import torch
     import torch.distributed as dist
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
-        return idxs, scores
+    local = np.ascontiguousarray(local, dtype=np.float32)
+    if not _is_dist():
+        return [local]
     world, rank = dist.get_world_size(), dist.get_rank()
     if device is None:
-        device = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
-    keys = sorted(scores.keys())
-    n_local = torch.tensor([idxs.shape[0]], dtype=torch.int64, device=device)
-    counts = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
-    dist.all_gather(counts, n_local)
-    counts = [int(c.item()) for c in counts]
-    nmax = max(max(counts), 1)
-    # one padded float64 block per rank: [i, j, score_0, score_1, ...]
-    block = np.zeros((nmax, 2 + len(keys)), dtype=np.float64)
-    block[:idxs.shape[0], 0:2] = idxs
-    for k, key in enumerate(keys):
-        block[:idxs.shape[0], 2 + k] = scores[key]
-    t = torch.from_numpy(block).to(device)
-    outs = [torch.empty_like(t) for _ in range(world)]
-    dist.all_gather(outs, t)  # NCCL has no gather-to-one on every version; all_gather is equivalent here
+        device = _default_device()
+    K = local.shape[0]
+    n = torch.tensor([local.shape[1]], dtype=torch.int64, device=device)
+    counts = _allgather(n).view(-1).cpu().numpy()
+    nmax = int(counts.max())
+    buf = torch.zeros((K, max(nmax, 1)), dtype=torch.float32, device=device)
+    buf[:, :local.shape[1]] = torch.from_numpy(local).to(device)
+    outs = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
+    dist.gather(buf, gather_list=outs, dst=dst)
     if rank != dst:
-        return None, None
-    parts = [o.cpu().numpy()[:c] for o, c in zip(outs, counts)]
-    allb = np.concatenate(parts, axis=0)
-    idxs_all = allb[:, 0:2].astype(np.int32)
-    scores_all = {key: allb[:, 2 + k].copy() for k, key in enumerate(keys)}
-    return idxs_all, scores_all
+        return None
+    return [o[:, :int(c)].cpu().numpy() for o, c in zip(outs, counts)]
 
 
-def all_pairwise_distributed(alg, T=128, symmetric=True):
-    """The multi-GPU form of CoverAlgorithm.all_pairwise (CoverAlgorithm.py:138-184): every rank
-    scores the pairs of its tiles, rank 0 assembles Ds, symmetrises and saves '<prefix>_Ds.h5'."""
+def place_tiles(Ds, keys, n_songs, T, tiles, shares, per_rank_scores):
+    """Drop every rank's score tiles into the N x N matrices Ds[key] (upper triangle; slicing, no fancy indexing)."""
+    for r, sc in enumerate(per_rank_scores):
+        off = 0
+        for t in shares[r]:
+            a, b = tiles[t]
+            i0, i1 = a * T, min((a + 1) * T, n_songs)
+            j0, j1 = b * T, min((b + 1) * T, n_songs)
+            if a != b:
+                cnt = (i1 - i0) * (j1 - j0)
+                for k, key in enumerate(keys):
+                    Ds[key][i0:i1, j0:j1] = sc[k, off:off + cnt].reshape(i1 - i0, j1 - j0)
+            else:
+                n = i1 - i0
+                cnt = n * (n - 1) // 2
+                iu = np.triu_indices(n, 1)   # row-major (i < j): the order of tile_pairs
+                for k, key in enumerate(keys):
+                    blk = np.zeros((n, n), np.float32)
+                    blk[iu] = sc[k, off:off + cnt]
+                    Ds[key][i0:i1, i0:i1] = blk
+            off += cnt
+        assert off == sc.shape[1], "rank %d: %d scores for %d tile pairs" % (r, sc.shape[1], off)
+
+
+def all_pairwise_distributed(alg, T=128, symmetric=True, save=True):
+    """The multi-GPU form of CoverAlgorithm.all_pairwise (CoverAlgorithm.py:138-184): every rank loads its share of
+    the songs, the arena is all-gathered device-to-device, every rank scores the pairs of its tiles, rank 0 receives
+    float32 score tiles, assembles Ds, symmetrises (`Ds += Ds.T`) and saves '<prefix>_Ds.h5'.  Construct `alg` with
+    do_memmaps=True on rank 0 only.  Returns a dict of timings / balance figures (every rank)."""
     import torch.distributed as dist
     from . import hdf5io
+    if not symmetric:
+        raise ValueError("all_pairwise_distributed scores the upper triangle and mirrors it (symmetric=True); the "
+                         "reference's ordered-pair mode is single-process only")
     rank, world, _ = dist_env()
-    lengths = np.array([alg.load_features(i)['chroma'].shape[1] for i in range(alg.N)])
-    mine = shard_pairs(alg.N, lengths, world, rank, T=T, m=alg.m)
+    if rank != 0 and alg.do_memmaps:
+        raise ValueError("construct the plugin with do_memmaps=True on rank 0 only: every rank would truncate the same "
+                         "'<prefix>_<type>_dmat' files")
+    t0 = time.perf_counter()
+    s0, s1 = song_shares(alg.N, world)[rank]
+    kinds = alg.share_songs_allgather(range(s0, s1))        # features of MY songs -> all-gather -> device arenas
+    t_share = time.perf_counter() - t0
+    lengths = alg.arena_lengths()
+    tiles, shares, load = shard_tiles(alg.N, lengths, world, T=T, m=alg.m)
+    mine = [tile_pairs(alg.N, T, tiles[t]) for t in shares[rank]]
+    mine = np.concatenate(mine, axis=0) if mine else np.zeros((0, 2), np.int32)
+    t1 = time.perf_counter()
     sims = alg.similarity(mine)
-    idxs_all, sims_all = gather_scores(mine, sims)
+    t_score = time.perf_counter() - t1
+    keys = sorted(sims.keys())
+    t2 = time.perf_counter()
+    local = np.stack([sims[k].astype(np.float32) for k in keys]) if keys else np.zeros((0, len(mine)), np.float32)
+    gathered = gather_score_tiles(local)
+    t_gather = time.perf_counter() - t2
     if rank == 0:
-        for key, v in sims_all.items():
-            if key in alg.Ds:
-                alg.Ds[key][idxs_all[:, 0], idxs_all[:, 1]] = v
+        place_tiles(alg.Ds, [k for k in keys if k in alg.Ds], alg.N, T, tiles, shares,
+                    [g[[i for i, k in enumerate(keys) if k in alg.Ds]] for g in gathered])
         alg.get_all_clique_ids()
-        if symmetric:
-            for key in alg.Ds:
-                alg.Ds[key] += alg.Ds[key].T
-        hdf5io.save("%s_Ds.h5" % alg.get_cacheprefix(), {k: np.asarray(v) for k, v in alg.Ds.items()})
-    if world > 1 and dist.is_initialized():
+        for key in alg.Ds:
+            alg.Ds[key] += alg.Ds[key].T
+        if save:
+            hdf5io.save("%s_Ds.h5" % alg.get_cacheprefix(), {k: np.asarray(v) for k, v in alg.Ds.items()})
+    if _is_dist():
         dist.barrier()
-    return sims
+    return {"kinds": kinds, "pairs_local": int(len(mine)), "share_songs_s": t_share, "score_s": t_score, "gather_s": t_gather,
+            "total_s": time.perf_counter() - t0, "lpt_imbalance": float(load.max() / max(load.mean(), 1e-30)),
+            "tiles": len(tiles)}

@@ -171,6 +171,48 @@ class Serra09(CoverAlgorithm):
         self._ctx[kind] = (ctx, slot)
         return ctx, slot
 
+    # ------------------------------------------------------------------ multi-GPU arena (acoss_b200.parallel)
+    def pack_shard(self, song_ids, kind):
+        """Host arena (pinned when a GPU is present) of the given songs only: (frames, lengths, gchroma or None)."""
+        song_ids = [int(i) for i in song_ids]
+        self.load_features_batch(song_ids)
+        songs = []
+        for i in song_ids:
+            f = self.load_features(i)
+            if kind == 'chroma':
+                songs.append({'chroma': np.asarray(f['chroma']), 'gchroma': f['gchroma']})
+            else:
+                songs.append({'chroma': np.asarray(f['mfcc']), 'gchroma': None})
+        if not songs:
+            bins = 12 if kind == 'chroma' else 13
+            return np.zeros((0, bins), np.float32), np.zeros(0, np.int32), (np.zeros((0, bins)) if kind == 'chroma' else None)
+        frames, _, lengths, g = _native.pack_songs(songs, pinned=True)
+        return frames, lengths, g
+
+    def share_songs_allgather(self, my_song_ids):
+        """Every rank contributes the features of its own songs; one all_gather per feature kind leaves the whole
+        arena in this rank's device memory, which the C ABI adopts device-to-device.  Returns the kinds shared."""
+        from . import parallel
+        my_song_ids = list(my_song_ids)
+        kinds = ['chroma']
+        if self.do_mfcc and (not my_song_ids or self.load_features(my_song_ids[0])['mfcc'] is not None):
+            kinds.append('mfcc')
+        for kind in kinds:
+            arena = parallel.allgather_songs(self.pack_shard(my_song_ids, kind))
+            entry = self._ctx.get(kind)
+            ctx = entry[0] if entry is not None else _native.Context(self.device)
+            arena.upload_into(ctx)
+            self._ctx[kind] = (ctx, np.arange(self.N, dtype=np.int64))
+            self._arena_lengths = np.asarray(arena.lengths)
+        self._shared_kinds = kinds
+        return kinds
+
+    def arena_lengths(self):
+        """Frames per song of the resident arena (after share_songs_allgather / preload)."""
+        if getattr(self, '_arena_lengths', None) is not None:
+            return self._arena_lengths
+        return np.array([self.load_features(i)['chroma'].shape[1] for i in range(self.N)])
+
     def preload(self, song_ids=None):
         """Upload the features of song_ids (default: all songs) ahead of scoring."""
         ids = np.arange(self.N) if song_ids is None else song_ids
@@ -189,7 +231,9 @@ class Serra09(CoverAlgorithm):
         if N == 0:
             return {s: np.zeros(0) for s in self.similarity_types}
         kinds = [('chroma', 0)]
-        if self.do_mfcc and self.load_features(int(idxs[0, 0]))['mfcc'] is not None:
+        shared = getattr(self, '_shared_kinds', None)
+        if (('mfcc' in shared) if shared is not None else
+                (self.do_mfcc and self.load_features(int(idxs[0, 0]))['mfcc'] is not None)):
             kinds.append(('mfcc', _native.FLAG_NO_OTI))   # Serra09.py:177-184: no OTI for mfcc
         stage = {}
         for kind, flags in kinds:

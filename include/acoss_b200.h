@@ -79,6 +79,9 @@ int acoss_destroy(acoss_ctx* ctx);
  * reference's (bins, L) array, so no transposition happens on the device).
  * gchroma: [n_songs][bins] float64 (Serra09.py:24-28,101-102) or NULL when every call
  * will pass ACOSS_FLAG_NO_OTI.  bins <= 16.
+ * `frames` and `gchroma` may be HOST or DEVICE pointers (e.g. the arena a multi-GPU run has just
+ * all-gathered over NCCL: the copy is then device-to-device, no host bounce); the caller makes sure
+ * the producer of a device buffer has finished.  offsets and lengths are always host arrays.
  */
 int acoss_upload_songs(acoss_ctx* ctx, const void* frames, int dtype,
                        const int64_t* offsets, const int32_t* lengths,
