@@ -36,7 +36,10 @@ def _run(ctx, spec, pairs, flag_sets, do_oti=True, nonmutual=False, max_tied=0):
         total_diff = max(total_diff, tied_diff)
     print("\n[wide parity] %s: %d pairs x %d flag sets bit-exact; %d tied pairs (relative neighbour gap < 1e-9) were "
           "only counted, %d of them differ" % (spec[0:2], len(pairs) - total_tied, len(flag_sets), total_tied, total_diff))
-    assert total_tied <= max(max_tied, len(pairs) // 500)   # <= 0.2 % of the pairs may be too close to call
+    # pairs too close to call (long songs have thousands of rows and columns, each with its own k-th / (k+1)-th gap):
+    # at most 1 % of the pairs, and at most 0.2 % may actually differ from the oracle's choice
+    assert total_tied <= max(max_tied, len(pairs) // 100)
+    assert total_diff <= max(max_tied, len(pairs) // 500)
     return total_tied
 
 
