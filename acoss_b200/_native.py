@@ -60,6 +60,8 @@ SIGNATURES = {
     "acoss_reset_counters": (None, [ctypes.c_void_p]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
+    "acoss_dp_packed_static": (ctypes.c_int, [ctypes.c_int32, ctypes.c_void_p, _c_i64p, _c_i32p, _c_i32p, ctypes.c_int32,
+                                              ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
     "acoss_debug_sweep7_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
 }
 
@@ -396,6 +398,20 @@ class Context:
         out = np.zeros(5, np.float32)
         self._check(self.lib.acoss_last_stage_ms(self._h, _ptr(out, _c_f32p)), "acoss_last_stage_ms")
         return dict(zip(["oti", "thresholds", "crp", "dp", "total"], out.tolist()))
+
+
+def dp_packed_static(lib, device, crp_ptr, crp_offsets, rows, cols, out_ptr, flags=0, stream=0):
+    """acoss_dp_packed_static: the DPs over packed plots that already live in DEVICE memory (crp_ptr / out_ptr are
+    device addresses, e.g. torch tensors' data_ptr(); out holds 3 * B floats: qmax | dmax | sw), no allocation and no
+    synchronisation inside the call.  Raises AcossError with the library's message on failure."""
+    crp_offsets = np.ascontiguousarray(crp_offsets, dtype=np.int64)
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    cols = np.ascontiguousarray(cols, dtype=np.int32)
+    rc = lib.acoss_dp_packed_static(int(device), ctypes.c_void_p(int(crp_ptr)), _ptr(crp_offsets, _c_i64p), _ptr(rows, _c_i32p),
+                                    _ptr(cols, _c_i32p), int(len(rows)), int(flags), ctypes.c_void_p(int(out_ptr)),
+                                    ctypes.c_void_p(int(stream)) if stream else None)
+    if rc != 0:
+        raise AcossError("acoss_dp_packed_static failed (%d): %s" % (rc, lib.acoss_last_error().decode()))
 
 
 def eval_layout(cliques):

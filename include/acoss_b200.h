@@ -128,6 +128,29 @@ int acoss_dp_packed(acoss_ctx* ctx, const uint32_t* crp, const int64_t* crp_offs
                     uint32_t flags, float* out);
 
 /*
+ * acoss_dp_packed for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * The entry point calls no cudaMalloc / cudaFree / allocating library routine and copies nothing between host and
+ * device: its scratch (plot records, item list, column-block hand-over records) is one file-scope __device__ array
+ * of 4 202 496 bytes (csrc/noalloc.cu) that every GPU loading the library holds until the process exits.
+ *   crp_dev   DEVICE pointer, packed plots (bit t of word w of row r = S[r][32 w + t]); plot b starts at word
+ *             crp_offsets[b] and has rows[b] x ceil(cols[b] / 32) words
+ *   crp_offsets, rows, cols   HOST arrays of B entries (read before the call returns)
+ *   out_dev   DEVICE pointer to 3 * B floats: [0, B) qmax, [B, 2B) dmax, [2B, 3B) sw (0 without
+ *             ACOSS_FLAG_WANT_SW); same values as acoss_dp_packed gives for the same plots and flags
+ *   stream    a cudaStream_t (NULL = the default stream); the call only enqueues two kernels on it and does not
+ *             synchronise: the caller waits on the stream before reading out_dev
+ * Limits (ACOSS_ERR_ARG beyond them): B <= 64 plots per call, rows and cols <= 16384, and at most 65536 rows in
+ * total over the plots wider than 128 columns.  Every call on a device shares the array, which keeps the previous
+ * call's contents (what must be fresh is rewritten by the call itself): calls that overlap on the GPU race, so
+ * serialise them.  The first call on a device also looks up the array's device address (cudaGetSymbolAddress);
+ * make that call outside a graph capture.
+ */
+int acoss_dp_packed_static(int32_t device, const uint32_t* crp_dev, const int64_t* crp_offsets,
+                           const int32_t* rows, const int32_t* cols, int32_t B,
+                           uint32_t flags, float* out_dev, void* stream);
+
+/*
  * Drop-in equivalents of pySeqAlign.qmax / dmax / swconstrained (pySeqAlign.pyx:7-23):
  * S is the unpacked uint8 matrix, row-major.  qmax/dmax: S is M x N (rows, cols);
  * swconstrained: S is N x M (its first int is the row count, as in
