@@ -262,6 +262,37 @@ def place_tiles(Ds, keys, n_songs, T, tiles, shares, per_rank_scores):
         assert off == sc.shape[1], "rank %d: %d scores for %d tile pairs" % (r, sc.shape[1], off)
 
 
+def score_tiles(alg, tile_ids, T, tiles=None, lengths=None, place=True):
+    """One distributed pass over a subset of the tile list (songs must already be resident: share_songs_allgather /
+    preload): the tiles are dealt to the ranks by estimated cost, every rank scores the pairs of its tiles, the float32
+    score tiles are gathered on rank 0 and (place=True) dropped into alg.Ds there.  Returns a dict of figures."""
+    rank, world, _ = dist_env()
+    lengths = alg.arena_lengths() if lengths is None else lengths
+    tiles = tile_list(alg.N, T) if tiles is None else tiles
+    sub = [tiles[int(t)] for t in tile_ids]
+    shares, load = assign_tiles(tile_costs(lengths, T, sub, alg.m), world)
+    mine = [tile_pairs(alg.N, T, sub[t]) for t in shares[rank]]
+    mine = np.concatenate(mine, axis=0) if mine else np.zeros((0, 2), np.int32)
+    t1 = time.perf_counter()
+    alg._defer_store = True   # rank 0 places whole tiles below; no per-pair scatter inside similarity()
+    try:
+        sims = alg.similarity(mine) if len(mine) else {k: np.zeros(0) for k in alg.similarity_types}
+    finally:
+        alg._defer_store = False
+    t_score = time.perf_counter() - t1
+    keys = sorted(sims.keys())
+    t2 = time.perf_counter()
+    local = np.stack([sims[k].astype(np.float32) for k in keys]) if keys else np.zeros((0, len(mine)), np.float32)
+    gathered = gather_score_tiles(local)
+    if rank == 0 and place and len(alg.Ds):
+        have = [i for i, k in enumerate(keys) if k in alg.Ds]
+        place_tiles(alg.Ds, [keys[i] for i in have], alg.N, T, sub, shares, [g[have] for g in gathered])
+    t_gather = time.perf_counter() - t2
+    return {"pairs_local": int(len(mine)), "pairs_total": int(sum(tile_pair_count(alg.N, T, t) for t in sub)),
+            "score_s": t_score, "gather_place_s": t_gather, "lpt_imbalance": float(load.max() / max(load.mean(), 1e-30)),
+            "tiles": len(sub), "keys": keys, "pairs_mine": mine}
+
+
 def all_pairwise_distributed(alg, T=128, symmetric=True, save=True):
     """The multi-GPU form of CoverAlgorithm.all_pairwise (CoverAlgorithm.py:138-184): every rank loads its share of
     the songs, the arena is all-gathered device-to-device, every rank scores the pairs of its tiles, rank 0 receives
@@ -280,21 +311,9 @@ def all_pairwise_distributed(alg, T=128, symmetric=True, save=True):
     s0, s1 = song_shares(alg.N, world)[rank]
     kinds = alg.share_songs_allgather(range(s0, s1))        # features of MY songs -> all-gather -> device arenas
     t_share = time.perf_counter() - t0
-    lengths = alg.arena_lengths()
-    tiles, shares, load = shard_tiles(alg.N, lengths, world, T=T, m=alg.m)
-    mine = [tile_pairs(alg.N, T, tiles[t]) for t in shares[rank]]
-    mine = np.concatenate(mine, axis=0) if mine else np.zeros((0, 2), np.int32)
-    t1 = time.perf_counter()
-    sims = alg.similarity(mine)
-    t_score = time.perf_counter() - t1
-    keys = sorted(sims.keys())
-    t2 = time.perf_counter()
-    local = np.stack([sims[k].astype(np.float32) for k in keys]) if keys else np.zeros((0, len(mine)), np.float32)
-    gathered = gather_score_tiles(local)
-    t_gather = time.perf_counter() - t2
+    tiles = tile_list(alg.N, T)
+    info = score_tiles(alg, range(len(tiles)), T, tiles)
     if rank == 0:
-        place_tiles(alg.Ds, [k for k in keys if k in alg.Ds], alg.N, T, tiles, shares,
-                    [g[[i for i, k in enumerate(keys) if k in alg.Ds]] for g in gathered])
         alg.get_all_clique_ids()
         for key in alg.Ds:
             alg.Ds[key] += alg.Ds[key].T
@@ -302,6 +321,6 @@ def all_pairwise_distributed(alg, T=128, symmetric=True, save=True):
             hdf5io.save("%s_Ds.h5" % alg.get_cacheprefix(), {k: np.asarray(v) for k, v in alg.Ds.items()})
     if _is_dist():
         dist.barrier()
-    return {"kinds": kinds, "pairs_local": int(len(mine)), "share_songs_s": t_share, "score_s": t_score, "gather_s": t_gather,
-            "total_s": time.perf_counter() - t0, "lpt_imbalance": float(load.max() / max(load.mean(), 1e-30)),
-            "tiles": len(tiles)}
+    info.pop("pairs_mine")
+    info.update({"kinds": kinds, "share_songs_s": t_share, "total_s": time.perf_counter() - t0})
+    return info

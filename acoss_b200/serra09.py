@@ -197,8 +197,14 @@ class Serra09(CoverAlgorithm):
         kinds = ['chroma']
         if self.do_mfcc and (not my_song_ids or self.load_features(my_song_ids[0])['mfcc'] is not None):
             kinds.append('mfcc')
+        if not hasattr(self, '_shards'):
+            self._shards = {}   # kind -> (song ids, packed pinned host shard): packed once, re-uploaded every call
         for kind in kinds:
-            arena = parallel.allgather_songs(self.pack_shard(my_song_ids, kind))
+            cached = self._shards.get(kind)
+            if cached is None or cached[0] != my_song_ids:
+                cached = (my_song_ids, self.pack_shard(my_song_ids, kind))
+                self._shards[kind] = cached
+            arena = parallel.allgather_songs(cached[1])
             entry = self._ctx.get(kind)
             ctx = entry[0] if entry is not None else _native.Context(self.device)
             arena.upload_into(ctx)
@@ -246,7 +252,7 @@ class Serra09(CoverAlgorithm):
             similarities['%s_dmax' % kind] = r['dmax_raw'].astype(np.float64) / MN
             stage[kind] = ctx.last_stage_ms()
         self.last_stage_ms = stage
-        if self.do_memmaps or len(self.Ds) > 0:
+        if (self.do_memmaps or len(self.Ds) > 0) and not getattr(self, '_defer_store', False):
             for key in similarities:
                 if key in self.Ds:
                     self.Ds[key][idxs[:, 0], idxs[:, 1]] = similarities[key]
@@ -259,7 +265,8 @@ class Serra09(CoverAlgorithm):
             self._ctx[kind] = (ctx, -np.ones(self.N, dtype=np.int64))
 
     def host_arena_bytes(self):
-        return sum(sum(a.nbytes for a in packed if a is not None) for _, packed in self._packed.values())
+        n = sum(sum(a.nbytes for a in packed if a is not None) for _, packed in self._packed.values())
+        return n + sum(sum(a.nbytes for a in shard if a is not None) for _, shard in getattr(self, '_shards', {}).values())
 
     def kernel_launches(self):
         return sum(ctx.kernel_launches() for ctx, _ in self._ctx.values())

@@ -3,18 +3,22 @@
 
   python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
   python bench.py --impl reference --gpus N --steps K --warmup W
+  python bench.py --config benchmark ...                   (BASELINE configs[2]: 15 000 songs, cliques of 13)
+  python bench.py --config benchmark --full-job            (the whole 112 492 500-pair matrix once; not a bench line)
 
-Workload (config.workload): BASELINE configs[1], the whatisacover-subset-shaped synthetic HPCP
-set (10 000 songs, 5000 cliques x 2, seed 10000, lengths lognormal around 450 frames), m = 9,
-kappa = 0.095.  A STEP is one pass of the hot path (OTI -> cross-similarity -> mutual-kNN CRP
--> Qmax + Dmax) over one batch of song pairs drawn uniformly (seeded) from the all-pairs list;
-every step scores a different batch and the float64 song arena (~0.45 GB) is larger than L2.
-At N > 1 each rank scores its own batch of the same size (weak scaling, no data-path
-collective: pairs are independent); `value` = all ranks' pairs / max-over-ranks time.
+Workload (config.workload): by default BASELINE configs[1], the whatisacover-subset-shaped synthetic HPCP set
+(10 000 songs, 5000 cliques x 2, seed 10000, lengths lognormal around 450 frames), m = 9, kappa = 0.095.
+The all-pairs matrix is cut into T x T song tiles (acoss_b200.parallel: upper triangle, T = 32 here).  A STEP is one
+pass of the hot path (OTI -> cross-similarity -> mutual-kNN CRP -> Qmax + Dmax) over a fixed-size set of tiles
+(--pairs-per-step pairs IN TOTAL, a different seeded tile set every step); the float64 song arena (~0.45 GB) is
+larger than L2.  STRONG scaling: at N > 1 the SAME tile set is dealt to the N ranks by estimated cost
+(longest-processing-time greedy), `value` = the step's pairs / max-over-ranks time.  No data-path collective:
+pairs are independent.
 
-`value` times the C-ABI call with the songs already resident in HBM; `e2e` times the plugin call
-(Serra09.similarity) with the host->device copy of the song arena from pinned host memory, the
-pair list and the device->host read of the scores inside the timed region.
+`value` times the C-ABI call with the songs already resident in HBM.  `e2e` times the plugin-level distributed pass
+with HOST buffers: every step each rank copies ITS shard of the songs from pinned host memory to its device, the
+shards are all-gathered over NCCL (device to device), every rank scores its tiles, the float32 score tiles are
+gathered on rank 0, read back and placed in the host N x N matrices.
 """
 import os
 
@@ -39,30 +43,45 @@ FP64_LANES_PER_SM = 64   # B200: FP64 SIMT at half the FP32 rate
 N_SM = 148
 
 
+CONFIGS = {
+    # name: (synth shape, songs, seed, description)
+    "whatisacover": ("whatisacover", 10000, 10000, "whatisacover-subset-shaped synthetic HPCP (BASELINE configs[1])"),
+    "benchmark": ("benchmark", 15000, 15000, "Da-TACOS benchmark-subset-shaped synthetic HPCP (BASELINE configs[2]: 1000 cliques x 13 + 2000 singletons)"),
+}
+TILE = 32  # song tile edge of the bench's pair tiles (1024 pairs per off-diagonal tile)
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=("b200", "reference"), default="b200")
-    ap.add_argument("--songs", type=int, default=10000, help="songs of the whatisacover-shaped set")
-    ap.add_argument("--pairs-per-step", type=int, default=200000, help="pairs per rank per step")
+    ap.add_argument("--config", choices=sorted(CONFIGS), default="whatisacover")
+    ap.add_argument("--songs", type=int, default=0, help="songs of the set (0: the config's own count)")
+    ap.add_argument("--pairs-per-step", type=int, default=800000, help="pairs per step, IN TOTAL over all GPUs (strong scaling)")
     ap.add_argument("--cpu-pairs", type=int, default=0,
                     help="pairs of the CPU sample (0: 800 per core in the default arm = 15-25 s of CPU work, "
                          "150 per core and step in the reference arm)")
-    ap.add_argument("--sweep-gen", type=int, default=0, help="force a sweep generation (2 .. 6); 0 = library default")
+    ap.add_argument("--sweep-gen", type=int, default=0, help="force a sweep generation (2, 4 .. 7); 0 = library default")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--mfcc", action="store_true", help="also time the default plugin call (chroma + mfcc halves) once")
+    ap.add_argument("--full-job", action="store_true", help="score the whole all-pairs matrix once and report its wall time")
+    args = ap.parse_args()
+    if not args.songs:
+        args.songs = CONFIGS[args.config][1]
+    return args
 
 
-def make_workload(n_songs):
+def make_workload(args):
     from acoss_b200 import synth
-    songs, labels = synth.make_song_set("whatisacover", seed=10000, n_songs=n_songs)
+    shape, _, seed, _ = CONFIGS[args.config]
+    songs, labels = synth.make_song_set(shape, seed=seed, n_songs=args.songs)
     return songs, labels
 
 
 def step_pairs(n_songs, per_step, step, rank, world, seed=4242):
-    """Batch of (i < j) pairs for (step, rank): uniform over the upper triangle, seeded."""
+    """Batch of (i < j) pairs for (step, rank): uniform over the upper triangle, seeded (CPU arm, experiments)."""
     rng = np.random.default_rng([seed, step, rank])
     i = rng.integers(0, n_songs, size=per_step + per_step // 8 + 16)
     j = rng.integers(0, n_songs, size=i.size)
@@ -70,6 +89,39 @@ def step_pairs(n_songs, per_step, step, rank, world, seed=4242):
     i, j = i[keep][:per_step], j[keep][:per_step]
     lo, hi = np.minimum(i, j), np.maximum(i, j)
     return np.stack([lo, hi], axis=1).astype(np.int32)
+
+
+class TileSets:
+    """Seeded tile subsets of the all-pairs tile list: step s scores tiles(s), about `per_step` pairs in total."""
+
+    def __init__(self, n_songs, lengths, per_step, T=TILE, seed=4242):
+        from acoss_b200 import parallel
+        self.par, self.n, self.T, self.per_step, self.seed, self.lengths = parallel, n_songs, T, per_step, seed, lengths
+        self.tiles = parallel.tile_list(n_songs, T)
+        nt = (n_songs + T - 1) // T
+        edge = np.minimum((np.arange(nt) + 1) * T, n_songs) - np.arange(nt) * T
+        a = np.array([t[0] for t in self.tiles]); b = np.array([t[1] for t in self.tiles])
+        self.count = np.where(a != b, edge[a] * edge[b], edge[a] * (edge[a] - 1) // 2)
+        self.costs = parallel.tile_costs(lengths, T, self.tiles, M_WIN)
+
+    def tile_ids(self, step):
+        rng = np.random.default_rng([self.seed, step])
+        perm = rng.permutation(len(self.tiles))
+        csum = np.cumsum(self.count[perm])
+        k = int(np.searchsorted(csum, self.per_step)) + 1
+        return np.sort(perm[:k])
+
+    def shares(self, step, world):
+        """(tile ids, per-rank index arrays into them, per-rank estimated load)"""
+        ids = self.tile_ids(step)
+        sh, load = self.par.assign_tiles(self.costs[ids], world)
+        return ids, sh, load
+
+    def rank_pairs(self, step, world, rank):
+        ids, sh, load = self.shares(step, world)
+        mine = [self.par.tile_pairs(self.n, self.T, self.tiles[ids[t]]) for t in sh[rank]]
+        pairs = np.concatenate(mine, axis=0) if mine else np.zeros((0, 2), np.int32)
+        return pairs, int(self.count[ids].sum()), float(load.max() / max(load.mean(), 1e-30))
 
 
 def pair_work(lengths, pairs, m=M_WIN):
@@ -173,7 +225,7 @@ def run_reference(args, rank, world):
     cores (rank 0 only).  Each step is a bounded sample of the same workload."""
     if rank != 0:
         return
-    songs, _ = make_workload(args.songs)
+    songs, _ = make_workload(args)
     lengths = np.array([s["chroma"].shape[1] for s in songs])
     cores = os.cpu_count() or 1
     n = args.cpu_pairs or max(64, 150 * cores)
@@ -190,8 +242,9 @@ def run_reference(args, rank, world):
     line = {
         "impl": "reference", "metric": "song_pairs_per_sec", "value": value, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, n),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_pairs_per_step": n,
         "qmax_gcups_whole_path": qcells / total / 1e9,
         "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": cores, "kind": "port",
                          "sample": cpu_sample_desc(n, cores) + "; per step"},
@@ -200,19 +253,21 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, pairs_per_step):
-    return {"workload": "whatisacover-subset-shaped synthetic HPCP (BASELINE configs[1]): %d songs, 12 bins, "
-                        "lognormal lengths median 450 frames, all-pairs list sampled uniformly" % args.songs,
-            "songs": args.songs, "pairs_per_step_per_gpu": pairs_per_step, "m": M_WIN, "kappa": KAPPA,
+def workload_config(args):
+    desc = CONFIGS[args.config][3]
+    return {"workload": "%s: %d songs, 12 bins, lognormal lengths median 450 frames; a step = a seeded set of %d x %d song "
+                        "tiles of the all-pairs matrix, about %d pairs in total, dealt to the GPUs by estimated cost"
+                        % (desc, args.songs, TILE, TILE, args.pairs_per_step),
+            "songs": args.songs, "pairs_per_step_total": args.pairs_per_step, "tile": TILE, "m": M_WIN, "kappa": KAPPA,
             "total_pairs_in_full_job": args.songs * (args.songs - 1) // 2,
-            "l2_policy": "inputs larger than L2 (0.45 GB float64 song arena, a new pair batch every step)"}
+            "l2_policy": "inputs larger than L2 (0.45 GB float64 song arena at 10 000 songs, a new tile set every step)"}
 
 
 # ---------------------------------------------------------------------------- B200 arm
 def run_b200(args, rank, world, local):
     import torch
     import torch.distributed as dist
-    from acoss_b200 import _native, parallel
+    from acoss_b200 import parallel
     from acoss_b200.serra09 import Serra09
 
     distributed = world > 1
@@ -223,42 +278,40 @@ def run_b200(args, rank, world, local):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # songs: generated on rank 0, shared once over NCCL (the run's only feature collective)
+    # Every rank builds the same seeded song set (in a real run: the feature files on shared storage) and keeps the
+    # features of ITS contiguous share for the all-gather; nothing is shipped from rank 0.
+    songs, labels = make_workload(args)
+    lengths = np.array([s["chroma"].shape[1] for s in songs])
+    N = len(songs)
     cpu_base = None
-    if rank == 0:
-        songs, labels = make_workload(args.songs)
-        packed = _native.pack_songs(songs, pinned=False)
-        if world == 1 and not args.no_cpu_baseline:
-            # CPU arm first: its worker processes are forked before this process touches CUDA
-            cores = os.cpu_count() or 1
-            n = args.cpu_pairs or max(64, 800 * cores)
-            secs = cpu_reference_run(songs, step_pairs(args.songs, n, 10_000, 0, 1), cores)
-            cpu_base = {"value": n / secs, "unit": "pairs/s", "cores": cores, "kind": "port",
-                        "sample": cpu_sample_desc(n, cores), "seconds": secs}
-    else:
-        songs, labels, packed = None, None, None
-    if distributed:
-        packed = parallel.broadcast_songs(packed, src=0)
-        if rank != 0:
-            frames, offs, lens, g = packed
-            songs = [{"chroma": np.ascontiguousarray(frames[o:o + n].T), "gchroma": g[k]}
-                     for k, (o, n) in enumerate(zip(offs, lens))]
-            labels = ["clique_%05d" % k for k in range(len(songs))]
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # CPU arm first: its worker processes are forked before this process touches CUDA
+        cores = os.cpu_count() or 1
+        n = args.cpu_pairs or max(64, 800 * cores)
+        secs = cpu_reference_run(songs, step_pairs(N, n, 10_000, 0, 1), cores)
+        cpu_base = {"value": n / secs, "unit": "pairs/s", "cores": cores, "kind": "port",
+                    "sample": cpu_sample_desc(n, cores), "seconds": secs}
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl b200 needs a CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local)
-    lengths = np.asarray(packed[2])
+    if distributed:
+        parallel.init_distributed()
     alg = Serra09(songs=songs, labels=labels, shortname="bench", do_memmaps=False, do_mfcc=False, device=local)
-    alg.preload()
-    ctx, slot = alg._context_for("chroma", np.arange(args.songs))
+    s0, s1 = parallel.song_shares(N, world)[rank]
+    alg.share_songs_allgather(range(s0, s1))   # songs resident on every GPU: shard H2D + all-gather + device-to-device
+    ctx = alg._ctx["chroma"][0]
     if args.sweep_gen:
         ctx.set_option("sweep_gen", args.sweep_gen)
-    B = args.pairs_per_step
+    ts = TileSets(N, lengths, args.pairs_per_step)
+    if args.full_job:
+        return run_full_job(args, alg, ts, rank, world, barrier)
 
-    # ---- value: C-ABI call, songs resident in HBM
+    # ---- value: C-ABI call, songs resident in HBM, this rank's tiles of the step's tile set
     for s in range(args.warmup):
-        ctx.serra09_pairs(step_pairs(args.songs, B, s, rank, world), m=M_WIN, kappa=KAPPA)
-    batches = [step_pairs(args.songs, B, args.warmup + s, rank, world) for s in range(args.steps)]
+        ctx.serra09_pairs(ts.rank_pairs(s, world, rank)[0], m=M_WIN, kappa=KAPPA)
+    batches = [ts.rank_pairs(args.warmup + s, world, rank) for s in range(args.steps)]
+    total_pairs = sum(b[1] for b in batches)
+    imbalance = float(np.mean([b[2] for b in batches]))
     sampler = ClockSampler(local)
     ctx.reset_counters()
     stage = {"oti": 0.0, "thresholds": 0.0, "crp": 0.0, "dp": 0.0, "total": 0.0}
@@ -266,87 +319,189 @@ def run_b200(args, rank, world, local):
     if rank == 0:
         sampler.start()
     t0 = time.perf_counter()
-    for pairs in batches:
+    for pairs, _, _ in batches:
         ctx.serra09_pairs(pairs, m=M_WIN, kappa=KAPPA)   # synchronises its stream before returning
         for k, v in ctx.last_stage_ms().items():
             stage[k] += v
+    busy = time.perf_counter() - t0                      # this rank's own time, before waiting for the others
     barrier()
     dt = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
     launches = ctx.kernel_launches()
 
-    # ---- e2e: plugin call, H2D of the song arena + pairs and D2H of the scores inside the region
-    for s in range(2):
-        alg.drop_device_arena()
-        alg.similarity(step_pairs(args.songs, B, 500 + s, rank, world))
-    e2e_batches = [step_pairs(args.songs, B, 600 + s, rank, world) for s in range(args.steps)]
+    # ---- e2e: the plugin-level distributed pass with HOST buffers, every step: this rank's song shard from pinned
+    # host memory -> device, all-gather (device to device), score my tiles, float32 tiles -> rank 0 -> host matrices
+    if rank == 0:
+        alg.Ds = {k: np.zeros((N, N), np.float32) for k in ("chroma_qmax", "chroma_dmax")}
+    e2e_sets = [ts.tile_ids(600 + s) for s in range(args.steps + 2)]
+    for ids in e2e_sets[:2]:
+        alg.share_songs_allgather(range(s0, s1))
+        parallel.score_tiles(alg, ids, TILE, ts.tiles, lengths)
+    share_s = gather_s = 0.0
+    e2e_pairs = 0
     barrier()
     t1 = time.perf_counter()
-    for pairs in e2e_batches:
-        alg.drop_device_arena()
-        sims = alg.similarity(pairs)
-        if distributed:
-            parallel.gather_scores(pairs, sims)   # score tiles back to rank 0
+    for ids in e2e_sets[2:]:
+        ta = time.perf_counter()
+        alg.share_songs_allgather(range(s0, s1))
+        share_s += time.perf_counter() - ta
+        info = parallel.score_tiles(alg, ids, TILE, ts.tiles, lengths)
+        gather_s += info["gather_place_s"]
+        e2e_pairs += info["pairs_total"]
     barrier()
     dt_e2e = time.perf_counter() - t1
+    return finish_b200(locals())
 
-    tmax = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
-    work = torch.tensor([float(x) for b in batches for x in pair_work(lengths, b)], dtype=torch.float64,
-                        device="cuda").reshape(-1, 3).sum(0)
-    if distributed:
+
+def default_plugin_rate(args, songs, labels, local, n_pairs=100000):
+    """The reference's default call computes chroma AND mfcc scores (Serra09.py:94,177-184): pairs/s of
+    Serra09(do_mfcc=True).similarity on synthetic 13-bin mfcc-like features of the same lengths (N = 1 only)."""
+    from acoss_b200.serra09 import Serra09
+    rng = np.random.default_rng(13)
+    both = []
+    for sgs in songs:
+        L = sgs["chroma"].shape[1]
+        fr = rng.normal(size=(L, 13)).cumsum(axis=0).astype(np.float32) * 0.1 + rng.normal(size=(L, 13)).astype(np.float32)
+        both.append({"chroma": sgs["chroma"], "gchroma": sgs["gchroma"], "mfcc": np.ascontiguousarray(fr.T)})
+    alg = Serra09(songs=both, labels=labels, shortname="bench_default", do_memmaps=False, do_mfcc=True, device=local)
+    alg.preload()
+    n = len(songs)
+    alg.similarity(step_pairs(n, n_pairs, 900, 0, 1))
+    t0 = time.perf_counter()
+    sims = alg.similarity(step_pairs(n, n_pairs, 901, 0, 1))
+    dt = time.perf_counter() - t0
+    out = {"value": n_pairs / dt, "unit": "pairs/s", "pairs": n_pairs, "similarity_types": sorted(sims.keys()),
+           "device_ms": {k: round(v["total"], 2) for k, v in alg.last_stage_ms.items()},
+           "note": "Serra09(do_mfcc=True).similarity(): chroma + mfcc halves, songs resident, one call; the 13-bin half "
+                   "runs on the same k_sweep7 kernels (K padded to 16 for the FP64 tensor-core fragments)"}
+    alg.close()
+    return out
+
+
+def run_full_job(args, alg, ts, rank, world, barrier):
+    """--full-job: the whole all-pairs matrix once (BASELINE's Target with --config benchmark), through
+    parallel.score_tiles in slabs of tiles; prints one JSON line with the wall time (not a bench line)."""
+    from acoss_b200 import parallel
+    N = alg.N
+    if rank == 0:
+        alg.Ds = {k: np.zeros((N, N), np.float32) for k in ("chroma_qmax", "chroma_dmax")}
+    T = 128
+    tiles = parallel.tile_list(N, T)
+    lengths = ts.lengths
+    slab = max(1, 4_000_000 // (T * T))          # ~4 M pairs per distributed pass
+    barrier()
+    t0 = time.perf_counter()
+    pairs = 0
+    score_s = gather_s = 0.0
+    imb = []
+    for a in range(0, len(tiles), slab):
+        info = parallel.score_tiles(alg, range(a, min(a + slab, len(tiles))), T, tiles, lengths)
+        pairs += info["pairs_total"]
+        score_s += info["score_s"]
+        gather_s += info["gather_place_s"]
+        imb.append(info["lpt_imbalance"])
+    barrier()
+    wall = time.perf_counter() - t0
+    if rank == 0:
+        for k in alg.Ds:
+            alg.Ds[k] += alg.Ds[k].T
+        q = alg.Ds["chroma_qmax"]
+        print(json.dumps({"full_job": True, "config": workload_config(args), "n_gpus": world, "pairs": pairs, "wall_s": wall,
+                          "pairs_per_sec": pairs / wall, "rank0_score_s": score_s, "rank0_gather_place_s": gather_s,
+                          "lpt_imbalance_mean": float(np.mean(imb)), "lpt_imbalance_max": float(np.max(imb)),
+                          "symmetric": bool(np.array_equal(q, q.T)), "nonzero_fraction": float((q > 0).mean()),
+                          "checksum_qmax": float(q.sum(dtype=np.float64))}), flush=True)
+    alg.close()
+
+
+def finish_b200(v):
+    import torch
+    import torch.distributed as dist
+    args, rank, world, local = v["args"], v["rank"], v["world"], v["local"]
+    alg, ctx, lengths, stage, batches = v["alg"], v["ctx"], v["lengths"], v["stage"], v["batches"]
+    tmax = torch.tensor([v["dt"], v["dt_e2e"], v["share_s"], v["gather_s"], v["busy"]], dtype=torch.float64, device="cuda")
+    tmin = torch.tensor([v["busy"]], dtype=torch.float64, device="cuda")
+    my = [float(sum(x)) for x in zip(*[pair_work(lengths, b[0]) for b in batches])]
+    work = torch.tensor(my + [float(v["launches"])], dtype=torch.float64, device="cuda")
+    if v["distributed"]:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
         dist.all_reduce(work, op=dist.ReduceOp.SUM)
-    dt, dt_e2e = float(tmax[0]), float(tmax[1])
-    cells, qcells, abytes = [float(x) for x in work]
+    dt, dt_e2e, share_s, gather_s, busy_max = [float(x) for x in tmax]
+    cells, qcells, abytes, launches = [float(x) for x in work]
     if rank != 0:
+        alg.close()
         return
-    total_pairs = B * args.steps * world
-    value = total_pairs / dt
-    e2e_value = total_pairs / dt_e2e
-    h2d = alg.host_arena_bytes() + B * 8
-    d2h = B * 20
-    # roofline of the dominant kernel group (k_sweep: thresholds x2 orientations + CRP), rank 0's launches
+    steps = args.steps
+    value = v["total_pairs"] / dt
+    e2e_value = v["e2e_pairs"] / dt_e2e
+    pairs_step = v["total_pairs"] / steps
+    h2d = int(sum(a.nbytes for a in alg._shards["chroma"][1] if a is not None) * world + pairs_step * 104)
+    d2h = int(pairs_step * 8 * (2 if world > 1 else 1))
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    my_cells, my_q, my_bytes = [float(sum(x)) for x in zip(*[pair_work(lengths, b) for b in batches])]
+    my_cells, my_q, my_bytes = my
     sweep_s = (stage["thresholds"] + stage["crp"]) / 1e3
+    clocks = v["clocks"]
     sm_max = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
     fp64_peak = N_SM * FP64_LANES_PER_SM * 2 * sm_max * 1e6 / 1e12
     achieved_tf = 26.0 * my_cells / sweep_s / 1e12 if sweep_s > 0 else None
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    traffic = None
+    try:  # DRAM bytes per pair of the sweep launches, from the ncu --set full capture of the same command
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r02_sweep_traffic.json")))
+        traffic = tj["dram_bytes_per_pair"] * (len(batches[0][0]) if batches else 0)
+    except Exception:
+        pass
+    dp_s = stage["dp"] / 1e3
+    int_peak_gcups = N_SM * 128 * sm_max * 1e6 / 4.0 / 1e9   # SURVEY 8d: >= 4 lane-ops per cell update, int32 lanes
+    dp_gcups = (2.0 * my_q / dp_s / 1e9) if dp_s > 0 else None
     line = {
-        "metric": "song_pairs_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, B),
+        "metric": "song_pairs_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args),
+        "pairs_per_step": pairs_step,
         "qmax_gcups_whole_path": qcells / dt / 1e9,
-        "qmax_dmax_gcups_dp_kernel": (2.0 * my_q / (stage["dp"] / 1e3) / 1e9) if stage["dp"] > 0 else None,
+        "qmax_dmax_gcups_dp_kernel": dp_gcups,
         "cells_per_sec": cells / dt,
-        "device_ms_per_step": {k: v / args.steps for k, v in stage.items()},
+        "device_ms_per_step": {k: x / steps for k, x in stage.items()},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": 1e3 * dt_e2e / args.steps},
+        "lpt_imbalance": v["imbalance"],
+        "rank_busy_ms_per_step": {"max": 1e3 * busy_max / steps, "min": 1e3 * float(tmin[0]) / steps},
+        "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": 1e3 * dt_e2e / steps, "share_songs_ms_per_step": 1e3 * share_s / steps,
+                "gather_place_ms_per_step": 1e3 * gather_s / steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
-                     "frac": (achieved_tf / fp64_peak) if achieved_tf else None, "traffic": None,
-                     "kernel": "k_sweep6 (FP64 tensor-core sweep: separators of one orientation + CRP of the other); "
-                               "k_sweep5 / k_sweep4 (FP64 SIMT) for column songs over 631 frames",
+                     "frac": (achieved_tf / fp64_peak) if achieved_tf else None, "traffic": traffic,
+                     "kernel": "k_sweep7 (FP64 tensor-core dot products + integer window sums + chained row selection: "
+                               "separators of one orientation, packed CRP of the other); k_sweep6/5/4 only for column "
+                               "songs over 1015 frames",
                      "note": "FP64 roofline, NOT the bf16 figure of MEASURED_PEAKS.json (which has no FP64 entry): "
                              "peak = 148 SM x 64 FP64 FMA/cycle x 2 x sm_max_mhz, the rate measured for both DMMA "
-                             "(mma.sync.m8n8k4.f64, profiles/exp/ubench/dmma_rate.cu: 16 cycles per instruction per SM "
-                             "sub-partition) and DFMA (profiles/exp/ubench/fp64_lat.cu); algorithmic 26 flop/cell counted "
-                             "ONCE although every cell is computed twice (once per orientation); achieved = flops of all "
-                             "sweep launches of the timed steps / their summed device time (CUDA events on the launching "
-                             "stream); the sweeps are bound by the integer selection, not by the FP64 pipe (DESIGN.md 7)"},
+                             "(mma.sync.m8n8k4.f64, profiles/exp/ubench/dmma_rate.cu) and DFMA; algorithmic 26 flop/cell "
+                             "counted ONCE although every cell is computed twice (once per orientation); achieved = flops "
+                             "of rank 0's sweep launches of the timed steps / their summed device time (CUDA events on "
+                             "the launching stream); traffic = DRAM bytes of the sweep launches for one step's pairs of "
+                             "rank 0 (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_sweep_traffic.json)"},
+        "roofline_dp": {"bound": "int-alu", "achieved": dp_gcups, "peak": int_peak_gcups, "unit": "GCUPS",
+                        "frac": (dp_gcups / int_peak_gcups) if dp_gcups else None, "kernel": "k_dp<4> (Qmax + Dmax cell updates)",
+                        "note": "peak = 148 SM x 128 int32 lanes x sm_max_mhz / 4 lane-ops per cell update (SURVEY.md 8d)"},
         "roofline_hbm": {"bound": "hbm", "achieved": (my_bytes / sweep_s / 1e9) if sweep_s > 0 else None, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (my_bytes / sweep_s / 1e9 / hbm_peak) if sweep_s > 0 else None,
                          "note": "compulsory bytes only (both songs' frames + scores); the path is compute-bound by design, "
                                  "a high number here would mean the CRP round-trips (peak: measured copy bandwidth)"},
     }
-    if cpu_base is not None:
-        line["cpu_baseline"] = cpu_base
+    if v["cpu_base"] is not None:
+        line["cpu_baseline"] = v["cpu_base"]
+    if world == 1:
+        try:
+            line["e2e_default_plugin"] = default_plugin_rate(args, v["songs"], v["labels"], local)
+        except Exception as e:  # the headline must not depend on this extra
+            line["e2e_default_plugin"] = {"error": repr(e)}
     print(json.dumps(line), flush=True)
     alg.close()
 
@@ -359,9 +514,6 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
-    if world > 1:
-        from acoss_b200 import parallel
-        parallel.init_distributed()
     run_b200(args, rank, world, local)
     if world > 1:
         import torch.distributed as dist

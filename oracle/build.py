@@ -39,7 +39,9 @@ def build_oracle(force: bool = False) -> str:
         if cc is None:
             raise RuntimeError("no C compiler found for the oracle")
         # strict IEEE: no -ffast-math, so the restatement is the plain recurrence
-        subprocess.check_call([cc, "-O2", "-std=c11", "-fPIC", "-shared", src, "-o", ORACLE_SO])
+        tmp = "%s.%d.tmp" % (ORACLE_SO, os.getpid())   # several worker processes may build at once: publish atomically
+        subprocess.check_call([cc, "-O2", "-std=c11", "-fPIC", "-shared", src, "-o", tmp])
+        os.replace(tmp, ORACLE_SO)
     return ORACLE_SO
 
 
@@ -51,7 +53,9 @@ def build_ref(force: bool = False) -> str | None:
     os.makedirs(REF_DIR, exist_ok=True)
     if force or _newer(REF_SRC, REF_SO):
         cc = shutil.which("gcc") or shutil.which("cc")
-        subprocess.check_call([cc, "-Ofast", "-x", "c", "-w", "-fPIC", "-shared", REF_SRC, "-o", REF_SO])
+        tmp = "%s.%d.tmp" % (REF_SO, os.getpid())
+        subprocess.check_call([cc, "-Ofast", "-x", "c", "-w", "-fPIC", "-shared", REF_SRC, "-o", tmp])
+        os.replace(tmp, REF_SO)
     return REF_SO
 
 
