@@ -27,6 +27,7 @@ os.environ.setdefault("OMP_NUM_THREADS", "1")
 os.environ.setdefault("MKL_NUM_THREADS", "1")
 
 import argparse  # noqa: E402
+import contextlib  # noqa: E402
 import json  # noqa: E402
 import subprocess  # noqa: E402
 import sys  # noqa: E402
@@ -59,7 +60,7 @@ def parse_args():
     ap.add_argument("--impl", choices=("b200", "reference"), default="b200")
     ap.add_argument("--config", choices=sorted(CONFIGS), default="whatisacover")
     ap.add_argument("--songs", type=int, default=0, help="songs of the set (0: the config's own count)")
-    ap.add_argument("--pairs-per-step", type=int, default=800000, help="pairs per step, IN TOTAL over all GPUs (strong scaling)")
+    ap.add_argument("--pairs-per-step", type=int, default=1200000, help="pairs per step, IN TOTAL over all GPUs (strong scaling)")
     ap.add_argument("--cpu-pairs", type=int, default=0,
                     help="pairs of the CPU sample (0: 800 per core in the default arm = 15-25 s of CPU work, "
                          "150 per core and step in the reference arm)")
@@ -296,7 +297,8 @@ def run_b200(args, rank, world, local):
     torch.cuda.set_device(local)
     if distributed:
         parallel.init_distributed()
-    alg = Serra09(songs=songs, labels=labels, shortname="bench", do_memmaps=False, do_mfcc=False, device=local)
+    with contextlib.redirect_stdout(sys.stderr):   # the plugin prints like the reference does; stdout carries ONE JSON line
+        alg = Serra09(songs=songs, labels=labels, shortname="bench", do_memmaps=False, do_mfcc=False, device=local)
     s0, s1 = parallel.song_shares(N, world)[rank]
     alg.share_songs_allgather(range(s0, s1))   # songs resident on every GPU: shard H2D + all-gather + device-to-device
     ctx = alg._ctx["chroma"][0]
@@ -363,7 +365,8 @@ def default_plugin_rate(args, songs, labels, local, n_pairs=100000):
         L = sgs["chroma"].shape[1]
         fr = rng.normal(size=(L, 13)).cumsum(axis=0).astype(np.float32) * 0.1 + rng.normal(size=(L, 13)).astype(np.float32)
         both.append({"chroma": sgs["chroma"], "gchroma": sgs["gchroma"], "mfcc": np.ascontiguousarray(fr.T)})
-    alg = Serra09(songs=both, labels=labels, shortname="bench_default", do_memmaps=False, do_mfcc=True, device=local)
+    with contextlib.redirect_stdout(sys.stderr):
+        alg = Serra09(songs=both, labels=labels, shortname="bench_default", do_memmaps=False, do_mfcc=True, device=local)
     alg.preload()
     n = len(songs)
     alg.similarity(step_pairs(n, n_pairs, 900, 0, 1))
