@@ -160,33 +160,59 @@ def tile_pairs(n_songs, T, tile):
     return np.stack([I[keep], J[keep]], axis=1).astype(np.int32)
 
 
+def tiles_pairs(n_songs, T, tiles):
+    """tile_pairs for a list of tiles, concatenated in list order; full off-diagonal tiles are enumerated in one
+    vectorised step (a per-step cost of the distributed pass: the reference's itertools.combinations)."""
+    if not len(tiles):
+        return np.zeros((0, 2), np.int32)
+    gi, gj = np.divmod(np.arange(T * T, dtype=np.int32), T)   # row-major (i, j) inside a full tile
+    out = [None] * len(tiles)
+    full = [k for k, (a, b) in enumerate(tiles) if a != b and (a + 1) * T <= n_songs and (b + 1) * T <= n_songs]
+    if full:
+        ab = np.array([tiles[k] for k in full], dtype=np.int32)
+        I = (ab[:, 0:1] * T + gi[None, :])
+        J = (ab[:, 1:2] * T + gj[None, :])
+        blk = np.stack([I, J], axis=2)                          # (n_full, T*T, 2)
+        for q, k in enumerate(full):
+            out[k] = blk[q]
+    for k in range(len(tiles)):
+        if out[k] is None:
+            out[k] = tile_pairs(n_songs, T, tiles[k])
+    return np.concatenate(out, axis=0).astype(np.int32, copy=False)
+
+
 def tile_costs(lengths, T, tiles, m=9):
     """Estimated work of each tile: sum over its pairs of M*N (cells of the cross-recurrence plot)."""
     w = np.maximum(np.asarray(lengths, dtype=np.float64) - m + 1, 0.0)
     n = len(w)
     nt = (n + T - 1) // T
-    s = np.array([w[a * T:(a + 1) * T].sum() for a in range(nt)])
-    s2 = np.array([(w[a * T:(a + 1) * T] ** 2).sum() for a in range(nt)])
-    costs = []
-    for a, b in tiles:
-        if a != b:
-            costs.append(s[a] * s[b])
-        else:
-            costs.append(0.5 * (s[a] ** 2 - s2[a]))
-    return np.array(costs)
+    pad = np.zeros(nt * T)
+    pad[:n] = w
+    s = pad.reshape(nt, T).sum(axis=1)
+    s2 = (pad.reshape(nt, T) ** 2).sum(axis=1)
+    if not len(tiles):
+        return np.zeros(0)
+    ab = np.asarray(tiles, dtype=np.int64).reshape(-1, 2)
+    a, b = ab[:, 0], ab[:, 1]
+    return np.where(a != b, s[a] * s[b], 0.5 * (s[a] ** 2 - s2[a]))
 
 
 def assign_tiles(costs, world):
-    """Longest-processing-time greedy: tiles by decreasing cost to the least-loaded rank.
+    """Longest-processing-time greedy: tiles by decreasing cost to the least-loaded rank (ties: lowest rank).
     Returns (list of tile-index arrays, one per rank, each in ascending tile order; per-rank load).  Deterministic
     on every rank."""
+    import heapq
     order = np.argsort(-costs, kind="stable")
-    load = np.zeros(world)
+    heap = [(0.0, r) for r in range(world)]
     owner = np.zeros(len(costs), dtype=np.int64)
-    for t in order:
-        r = int(np.argmin(load))
+    cl = costs.tolist()
+    for t in order.tolist():
+        load_r, r = heapq.heappop(heap)
         owner[t] = r
-        load[r] += costs[t]
+        heapq.heappush(heap, (load_r + cl[t], r))
+    load = np.zeros(world)
+    for load_r, r in heap:
+        load[r] = load_r
     return [np.nonzero(owner == r)[0] for r in range(world)], load
 
 
@@ -200,10 +226,7 @@ def shard_tiles(n_songs, lengths, world, T=128, m=9, tiles=None):
 def shard_pairs(n_songs, lengths, world, rank, T=128, m=9, tiles=None):
     """This rank's share of the all-pairs list: concatenated pairs of its tiles."""
     tiles, shares, _ = shard_tiles(n_songs, lengths, world, T, m, tiles)
-    mine = [tile_pairs(n_songs, T, tiles[t]) for t in shares[rank]]
-    if not mine:
-        return np.zeros((0, 2), np.int32)
-    return np.concatenate(mine, axis=0)
+    return tiles_pairs(n_songs, T, [tiles[t] for t in shares[rank]])
 
 
 def tile_pair_count(n_songs, T, tile):
@@ -271,8 +294,7 @@ def score_tiles(alg, tile_ids, T, tiles=None, lengths=None, place=True):
     tiles = tile_list(alg.N, T) if tiles is None else tiles
     sub = [tiles[int(t)] for t in tile_ids]
     shares, load = assign_tiles(tile_costs(lengths, T, sub, alg.m), world)
-    mine = [tile_pairs(alg.N, T, sub[t]) for t in shares[rank]]
-    mine = np.concatenate(mine, axis=0) if mine else np.zeros((0, 2), np.int32)
+    mine = tiles_pairs(alg.N, T, [sub[t] for t in shares[rank]])
     t1 = time.perf_counter()
     alg._defer_store = True   # rank 0 places whole tiles below; no per-pair scatter inside similarity()
     try:

@@ -120,8 +120,7 @@ class TileSets:
 
     def rank_pairs(self, step, world, rank):
         ids, sh, load = self.shares(step, world)
-        mine = [self.par.tile_pairs(self.n, self.T, self.tiles[ids[t]]) for t in sh[rank]]
-        pairs = np.concatenate(mine, axis=0) if mine else np.zeros((0, 2), np.int32)
+        pairs = self.par.tiles_pairs(self.n, self.T, [self.tiles[ids[t]] for t in sh[rank]])
         return pairs, int(self.count[ids].sum()), float(load.max() / max(load.mean(), 1e-30))
 
 
