@@ -467,7 +467,8 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             // gen 7 per orientation where the column song fits; both orientations of a pair must be served by
             // integer-key kernels (gens 4-7 share the separator format), which for 13 bins means gen 7 twice
             auto b7 = [&](int Lc) {
-                const int b = sweep7_bucket_for(Lc);
+                int b = sweep7_bucket_for(Lc);
+                if ((c->opt_debug_flags & (1u << 21)) && (b == 2 || b == 4 || b == 6)) ++b;  // A/B: capacities 128, 256, 512, 768, 1024 only
                 return (g7_ok && b >= 0 && acoss_sweep7_smem(b, BINS, 2) <= (size_t)c->max_smem) ? b : -1;
             };
             const bool keys12 = gen4_ok && std::max(w.Li, w.Lj) <= s4_max_cols(m);

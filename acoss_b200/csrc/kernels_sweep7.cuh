@@ -24,7 +24,8 @@
 //     leaves the SM once, as 1 bit per cell.
 //   * 13 bins (the mfcc half of Serra09.similarity, Serra09.py:177-184) run on the same kernel:
 //     K is padded to 16 for the DMMA fragments.
-//   * Column capacities 128 / 256 / 512 (one diagonal per thread) and 768 / 1024 (two).
+//   * Column capacities 128, 256, ..., 1024 in steps of 128 (the diagonal walk and the selection cost NC per row,
+//     whatever the song's length): one diagonal per thread up to 256 columns, two beyond.
 #pragma once
 #include <type_traits>
 
@@ -51,31 +52,24 @@ struct S7Cfg {
     static constexpr int NC = NT * CPT;                    // padded columns
     static constexpr int NW = NT / 32;
     static constexpr int NQ = NC / 128;                    // uint4 of a strip row per lane (selection: keys in registers)
-    // NC = 512 as 256 threads x 2 diagonals: two CTAs per SM (independent barrier domains), 32-row strips, one slab
-    static constexpr bool TWO = (NT == 256 && CPT == 2);
-    static constexpr int R = TWO ? 32 : (NC <= 512 ? 64 : (NC <= 768 ? 48 : 32));  // rows per strip
-    static constexpr bool DBS = NC <= 512 && !TWO;         // double-buffered slab
-    static constexpr int MINB = TWO ? 2 : (NC <= 128 ? 4 : (NC <= 256 ? 2 : 1));
+    // Rows per strip, slab buffering and CTAs per SM by column capacity (shared memory: R * NC * 4 bytes of keys):
+    //   128, 256            one diagonal per thread, 64-row strips, two slabs, 4 / 2 CTAs per SM
+    //   384, 512            two diagonals per thread (192 / 256 threads), 48 / 32-row strips, one slab, 2 CTAs per SM
+    //                       (independent barrier domains)
+    //   640                 320 threads x 2, 40-row strips, two slabs, 1 CTA per SM
+    //   768, 896, 1024      384 / 448 / 512 threads x 2, 48 / 32 / 32-row strips, one slab, 1 CTA per SM
+    //   512 as 512 x 1      measured alternative (debug flag): 64-row strips, two slabs, 1 CTA per SM
+    static constexpr bool WIDE1 = (NC == 512 && NT == 512);
+    static constexpr int R = (NC <= 256 || WIDE1) ? 64 : NC == 384 ? 48 : NC == 512 ? 32 : NC == 640 ? 40 : NC == 768 ? 48 : 32;
+    static constexpr bool DBS = NC <= 256 || WIDE1 || NC == 640;   // double-buffered slab
+    static constexpr int MINB = NC <= 128 ? 4 : ((NC <= 512 && NT <= 256) ? 2 : 1);
     static constexpr int LCP = NC + 8;                     // slab row stride (doubles), = 8 mod 16
     static constexpr int WPR = NC / 32;                    // CRP words per strip row
-    static constexpr int RPW = R / NW;                     // rows per warp: the chain resolved with lag-1 guesses
-    static_assert(NT % 32 == 0 && NC % 128 == 0 && R % (2 * kS7Per) == 0 && R % NW == 0, "shape");
+    static constexpr int RPW = (R + NW - 1) / NW;          // rows per warp: the chain resolved with lag-1 guesses
+    static_assert(NT % 32 == 0 && NC % 128 == 0 && R % kS7Per == 0 && R <= NT, "shape");
 };
 
-__host__ __device__ constexpr int s7_capacity_threads(int cap) {  // column capacity -> threads
-    return cap <= 512 ? cap : cap / 2;
-}
-__host__ __device__ constexpr int s7_capacity_of(int Lc) {
-    return Lc + kS7Pad <= 128 ? 128
-         : Lc + kS7Pad <= 256 ? 256
-         : Lc + kS7Pad <= 512 ? 512
-         : Lc + kS7Pad <= 768 ? 768
-         : Lc + kS7Pad <= 1024 ? 1024 : 0;
-}
-constexpr int kS7Buckets = 5;
-__host__ __device__ constexpr int s7_bucket_of(int cap) {
-    return cap == 128 ? 0 : cap == 256 ? 1 : cap == 512 ? 2 : cap == 768 ? 3 : 4;
-}
+constexpr int kS7Buckets = 8;                 // column capacities 128, 256, ..., 1024
 constexpr int kS7MaxCols = 1024 - kS7Pad;
 
 struct S7Layout {
@@ -486,8 +480,8 @@ __global__ void __launch_bounds__(NT, (S7Cfg<NT, CPT>::MINB)) k_sweep7(Sweep7Arg
 
             // ---- this warp's chain of RPW consecutive rows: separator, then (MODE 2) the row's CRP words
             if (nsel > 0 && (do_select || MODE == 2)) {
-                bool have_prev = false;
-                int prev_abs = 0;
+                bool have_prev = false, have_prev2 = false;
+                int prev_abs = 0, prev2_abs = 0;
 #pragma unroll 1
                 for (int q = 0; q < RPW; ++q) {
                     const int srow = warp * RPW + q;
@@ -499,17 +493,18 @@ __global__ void __launch_bounds__(NT, (S7Cfg<NT, CPT>::MINB)) k_sweep7(Sweep7Arg
                         const uint4* row4 = reinterpret_cast<const uint4*>(krow);
                         S4Keys<NQ> keys;
                         keys.load_strided(krow, lane);
-                        int t0 = prev_abs - kwx;
-                        bool have_g = have_prev;
-                        if (!have_prev) {
-                            const int ge = s4_estimate(keys, est_rank, lane);
-                            if (ge < kKeyInf - 1) {
-                                t0 = ge;
-                                have_g = true;
-                            }
+                        int vk, vk1, t0;
+                        bool have_g = true;
+                        if (have_prev) {
+                            // the previous row's separator, extrapolated by half the last step (absolute key units)
+                            t0 = prev_abs + (have_prev2 ? (prev_abs - prev2_abs) / 2 : 0) - kwx;
+                        } else {
+                            t0 = s4_estimate(keys, est_rank, lane);   // first row of the chain: from its own keys
+                            have_g = t0 < kKeyInf - 1;
                         }
-                        int vk, vk1;
                         s4_select(keys, kk, No, t0, have_g, st, lane, vk, vk1);
+                        have_prev2 = have_prev;
+                        prev2_abs = prev_abs;
                         const int gapk = vk1 - vk;
                         if (gapk >= 2 * G) {
                             thr = vk + (gapk >> 1);
@@ -565,7 +560,9 @@ __global__ void __launch_bounds__(NT, (S7Cfg<NT, CPT>::MINB)) k_sweep7(Sweep7Arg
             if (p + 1 < nper && !pre2) {
                 stage1(p + 1);
                 pre_done = true;
-                if (DBS && p + 2 < nper && ((p + 2) % PPS != 0)) {
+                // (not when period p + 2 starts a new block of staged rows: its prefetch would overwrite the rows that
+                // slower warps still need for period p + 1)
+                if (DBS && p + 2 < nper && ((p + 2) % PPS != 0) && (((p + 2) * kS7Per) & (kS4Stage - 1)) != 0) {
                     stage1(p + 2);  // both slabs are free behind the strip's last diagonal walk
                     pre2 = true;
                 }

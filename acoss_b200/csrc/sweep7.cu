@@ -45,17 +45,22 @@ int launch_one(acoss_ctx* c, const uint32_t* d_items, int n_items, unsigned int*
 
 template <int MODE, int BINS>
 int launch_bucket(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, unsigned int* d_counter, uint32_t flags, cudaStream_t stream) {
-    switch (bucket) {
+    switch (bucket) {  // capacity 128 * (bucket + 1) columns
         case 0: return launch_one<MODE, BINS, 128, 1>(c, d_items, n_items, d_counter, flags, stream);
         case 1: return launch_one<MODE, BINS, 256, 1>(c, d_items, n_items, d_counter, flags, stream);
-        case 2:
+        case 2: return launch_one<MODE, BINS, 192, 2>(c, d_items, n_items, d_counter, flags, stream);
+        case 3:
             if (c->opt_debug_flags & (1u << 20)) return launch_one<MODE, BINS, 512, 1>(c, d_items, n_items, d_counter, flags, stream);
             return launch_one<MODE, BINS, 256, 2>(c, d_items, n_items, d_counter, flags, stream);
-        case 3: return launch_one<MODE, BINS, 384, 2>(c, d_items, n_items, d_counter, flags, stream);
-        case 4: return launch_one<MODE, BINS, 512, 2>(c, d_items, n_items, d_counter, flags, stream);
+        case 4: return launch_one<MODE, BINS, 320, 2>(c, d_items, n_items, d_counter, flags, stream);
+        case 5: return launch_one<MODE, BINS, 384, 2>(c, d_items, n_items, d_counter, flags, stream);
+        case 6: return launch_one<MODE, BINS, 448, 2>(c, d_items, n_items, d_counter, flags, stream);
+        case 7: return launch_one<MODE, BINS, 512, 2>(c, d_items, n_items, d_counter, flags, stream);
     }
     return fail(ACOSS_ERR_ARG, "k_sweep7: no kernel for bucket %d", bucket);
 }
+
+static_assert(kSweep7Buckets == kS7Buckets && kSweep7Pad == kS7Pad && kSweep7MaxCols == kS7MaxCols, "sweep7.h mirrors kernels_sweep7.cuh");
 
 }  // namespace
 
@@ -73,8 +78,11 @@ size_t acoss_sweep7_smem(int bucket, int bins, int mode) {
     switch (bucket) {
         case 0: return (size_t)s7_layout<128, 1>(bins, mode).total;
         case 1: return (size_t)s7_layout<256, 1>(bins, mode).total;
-        case 2: return std::max((size_t)s7_layout<512, 1>(bins, mode).total, (size_t)s7_layout<256, 2>(bins, mode).total);
-        case 3: return (size_t)s7_layout<384, 2>(bins, mode).total;
+        case 2: return (size_t)s7_layout<192, 2>(bins, mode).total;
+        case 3: return std::max((size_t)s7_layout<512, 1>(bins, mode).total, (size_t)s7_layout<256, 2>(bins, mode).total);
+        case 4: return (size_t)s7_layout<320, 2>(bins, mode).total;
+        case 5: return (size_t)s7_layout<384, 2>(bins, mode).total;
+        case 6: return (size_t)s7_layout<448, 2>(bins, mode).total;
         default: return (size_t)s7_layout<512, 2>(bins, mode).total;
     }
 }

@@ -18,6 +18,7 @@ ctx.serra09_pairs(pairs)
 ctx.lib.acoss_debug_sweep7_stats(ctx._h, out, 0)
 v = [int(out[i]) for i in range(16)]
 calls = max(v[4], 1)
-print("rows %d unsafe %d | s4_select calls %d: counting passes/row %.2f walks/row %.2f failed walks/row %.3f boundary passes/row %.3f "
-      "bisections/row %.4f estimator calls/row %.3f no-guess starts/row %.4f" % (
+print("rows %d unsafe %d | selections %d: passes over the keys/row %.2f (fused + counting) candidate-pop rounds/row %.2f failed "
+      "pops/row %.3f boundary passes/row %.3f fallbacks to the bracketing search/row %.4f estimator calls/row %.3f "
+      "no-guess starts/row %.4f" % (
           v[0], v[1], v[4], v[5] / calls, v[6] / calls, v[7] / calls, v[8] / calls, v[9] / calls, v[10] / calls, v[11] / calls))

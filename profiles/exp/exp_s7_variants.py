@@ -18,6 +18,9 @@ ctx = _native.Context(0)
 ctx.upload_songs(songs)
 out = (ctypes.c_uint64 * 16)()
 ref = None
+if os.environ.get("ACOSS_GAP"):
+    ctx.set_option("gap_units", int(os.environ["ACOSS_GAP"]))
+    print("gap_units", os.environ["ACOSS_GAP"])
 for fl in flagsets:
     ctx.set_option("debug_flags", fl)
     for step in range(3):

@@ -59,11 +59,11 @@ def test_covers80_all_12720_pairs(ctx):
 
 
 def test_dispatch_buckets_m9(ctx):
-    """>= 200 pairs per column-song length class: the five capacities of the default sweep (128 / 256 / 512 / 768 / 1024
+    """>= 200 pairs per column-song length class: the eight capacities of the default sweep (128, 256, ..., 1024
     columns), the integer-key SIMT kernels (1016..1320), the float64 kernel (1321..1408) and the tiled path (> 1408);
     with and without the orientation swap so that both the separator sweep and the CRP sweep see every class."""
-    ranges = [(60, 119, 10), (120, 247, 10), (248, 503, 10), (504, 759, 10), (760, 1015, 10), (1016, 1320, 8),
-              (1321, 1408, 6), (1409, 1700, 4)]
+    ranges = [(60, 119, 8), (120, 247, 8), (248, 375, 8), (376, 503, 8), (504, 631, 8), (632, 759, 8), (760, 887, 8),
+              (888, 1015, 8), (1016, 1320, 8), (1321, 1408, 6), (1409, 1700, 4)]
     spec = ("ranges", 900, ranges)
     starts = np.cumsum([0] + [c for _, _, c in ranges])
     rng = np.random.default_rng(5)
