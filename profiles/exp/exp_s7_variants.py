@@ -25,6 +25,13 @@ for fl in flagsets:
     ctx.set_option("debug_flags", fl)
     for step in range(3):
         pairs = bench.step_pairs(10000, n_pairs, step, 0, 1)
+        if os.environ.get("ACOSS_MAXLEN"):   # drop the pairs with a song longer than this (cost of the long-song kernels)
+            Ls = np.array([sg["chroma"].shape[1] for sg in songs])
+            keep = (Ls[pairs[:, 0]] <= int(os.environ["ACOSS_MAXLEN"])) & (Ls[pairs[:, 1]] <= int(os.environ["ACOSS_MAXLEN"]))
+            if step == 2:
+                M = Ls[pairs] - 8
+                print("kept %.4f of the pairs, %.4f of the cells" % (keep.mean(), (M[keep, 0] * M[keep, 1]).sum() / (M[:, 0] * M[:, 1]).sum()))
+            pairs = pairs[keep]
         ctx.lib.acoss_debug_sweep7_stats(ctx._h, out, 1)
         r = ctx.serra09_pairs(pairs)
         ctx.lib.acoss_debug_sweep7_stats(ctx._h, out, 0)
