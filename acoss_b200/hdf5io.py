@@ -11,13 +11,19 @@ File layout produced (HDF5 file-format spec 1.x, the oldest and most widely read
   CLASS/VERSION/TITLE/FLAVOR attributes; str / int / float / bool scalars are attributes of
   the enclosing group, as deepdish stores them.
 The reader understands exactly those structures (plus object-header continuation blocks and
-multi-level group B-trees), i.e. it reads files written here and other plain contiguous HDF5
-files; chunked / compressed datasets (deepdish's default blosc CArrays) are reported as
-unsupported rather than misread.
+multi-level group B-trees) and, for files written by PyTables / deepdish / h5py, CHUNKED datasets
+(data layout class 2, v1 chunk B-trees of any depth) with the gzip (deflate, via the standard
+library's zlib), shuffle and fletcher32 filters -- what `dd.io.save(..., compression='zlib')` or
+`compression=None` produce.  blosc (deepdish's DEFAULT compressor, an HDF5 plug-in filter, id
+32001) and lzo / bzip2 cannot be decoded without their libraries: such files are rejected with a
+message that says how to re-export them.  No HDF5 library exists on either machine image, so
+interoperability with real libhdf5 output is restated from the file-format specification and
+checked only against files assembled by tests/test_host_logic.py: unpinned.
 """
 from __future__ import annotations
 
 import struct
+import zlib
 
 import numpy as np
 
@@ -25,7 +31,9 @@ UNDEF = 0xFFFFFFFFFFFFFFFF
 SIGNATURE = b"\x89HDF\r\n\x1a\n"
 INTERNAL_K = 16
 
-MSG_DATASPACE, MSG_DATATYPE, MSG_LAYOUT, MSG_ATTRIBUTE, MSG_CONT, MSG_SYMTAB = 0x1, 0x3, 0x8, 0xC, 0x10, 0x11
+MSG_DATASPACE, MSG_DATATYPE, MSG_LAYOUT, MSG_FILTERS, MSG_ATTRIBUTE, MSG_CONT, MSG_SYMTAB = 0x1, 0x3, 0x8, 0xB, 0xC, 0x10, 0x11
+FILTER_DEFLATE, FILTER_SHUFFLE, FILTER_FLETCHER32 = 1, 2, 3
+FILTER_NAMES = {4: "szip", 305: "lzo", 307: "bzip2", 32001: "blosc", 32004: "lz4", 32015: "zstd"}
 
 
 def _pad8(b: bytes) -> bytes:
@@ -91,9 +99,10 @@ def _object_header(messages) -> bytes:
 
 # ---------------------------------------------------------------------------- writer
 class _Writer:
-    def __init__(self, f, leaf_k):
+    def __init__(self, f, leaf_k, level=0):
         self.f = f
         self.leaf_k = leaf_k
+        self.level = int(level)   # 0: contiguous datasets; 1..9: chunked + shuffle + gzip at this level
 
     def _append(self, b: bytes) -> int:
         pos = self.f.tell()
@@ -103,6 +112,42 @@ class _Writer:
         self.f.write(b)
         return pos
 
+    def write_chunked(self, arr: np.ndarray) -> int:
+        """Chunked layout (whole leading-axis slabs of ~1 MiB) with the shuffle + gzip filters, one leaf chunk B-tree."""
+        item = arr.dtype.itemsize
+        row_bytes = max(int(np.prod(arr.shape[1:])) * item, 1)
+        crows = int(max(1, min(arr.shape[0], (1 << 20) // row_bytes)))
+        cshape = (crows,) + tuple(arr.shape[1:])
+        rank = arr.ndim
+        entries = []
+        for r0 in range(0, arr.shape[0], crows):
+            chunk = np.zeros(cshape, arr.dtype)
+            part = arr[r0:r0 + crows]
+            chunk[:part.shape[0]] = part
+            raw = np.frombuffer(chunk.tobytes(), np.uint8)
+            raw = raw.reshape(-1, item).T.reshape(-1).tobytes() if item > 1 else raw.tobytes()   # shuffle
+            comp = zlib.compress(raw, self.level)
+            addr = self._append(comp)
+            entries.append((len(comp), (r0,) + (0,) * (rank - 1) + (0,), addr))
+        if len(entries) > 0xFFFF:
+            raise ValueError("too many chunks for one B-tree node")
+        node = b"TREE" + struct.pack("<BBHQQ", 1, 0, len(entries), UNDEF, UNDEF)
+        for size, offs, addr in entries:
+            node += struct.pack("<II", size, 0) + b"".join(struct.pack("<Q", o) for o in offs) + struct.pack("<Q", addr)
+        last = tuple(-(-d // c) * c for d, c in zip(arr.shape, cshape)) + (0,)
+        node += struct.pack("<II", 0, 0) + b"".join(struct.pack("<Q", o) for o in last)
+        bt = self._append(node)
+        filt = struct.pack("<BB6x", 1, 2)
+        filt += struct.pack("<HHHH", FILTER_SHUFFLE, 0, 0, 1) + struct.pack("<II", item, 0)
+        filt += struct.pack("<HHHH", FILTER_DEFLATE, 0, 0, 1) + struct.pack("<II", self.level, 0)
+        layout = struct.pack("<BBB", 3, 2, rank + 1) + struct.pack("<Q", bt) + b"".join(
+            struct.pack("<I", d) for d in cshape + (item,))
+        msgs = [_message(MSG_DATASPACE, _dataspace_msg(arr.shape)), _message(MSG_DATATYPE, _datatype_msg(arr.dtype)),
+                _message(MSG_FILTERS, filt), _message(MSG_LAYOUT, layout),
+                _attribute_msg("CLASS", "CARRAY"), _attribute_msg("VERSION", "1.1"),
+                _attribute_msg("TITLE", ""), _attribute_msg("FLAVOR", "numpy")]
+        return self._append(_object_header(msgs))
+
     def write_dataset(self, arr: np.ndarray) -> int:
         arr = np.asarray(arr)
         if arr.dtype.kind == "U":
@@ -111,6 +156,8 @@ class _Writer:
             arr = arr.astype(arr.dtype.newbyteorder("<"))
         if not arr.flags.c_contiguous:
             arr = np.ascontiguousarray(arr)
+        if self.level and arr.ndim >= 1 and arr.size > 0 and arr.dtype.kind in "fiub":
+            return self.write_chunked(arr)
         nbytes = arr.size * arr.dtype.itemsize
         addr = UNDEF
         if nbytes:
@@ -185,8 +232,15 @@ def _max_entries(d):
     return n
 
 
-def save(path, data: dict):
-    """Write a (nested) dict of numpy arrays / scalars / strings to an HDF5 file."""
+def save(path, data: dict, compression=None):
+    """Write a (nested) dict of numpy arrays / scalars / strings to an HDF5 file.  compression: None (contiguous
+    datasets, memory-mappable), 'zlib' or ('zlib', level): chunked datasets with the shuffle + gzip filters, the
+    form deepdish / PyTables write with compression='zlib'."""
+    level = 0
+    if compression is not None:
+        name, level = (compression, 6) if isinstance(compression, str) else compression
+        if name not in ("zlib", "gzip"):
+            raise ValueError("compression must be None, 'zlib' or ('zlib', level); %r needs its own library" % (name,))
     if not isinstance(data, dict):
         raise TypeError("top level must be a dict (deepdish stores a dict as the root group's children)")
     leaf_k = max(4, (_max_entries(data) + 1) // 2)
@@ -194,7 +248,7 @@ def save(path, data: dict):
         raise ValueError("too many entries in one group")
     with open(path, "wb") as f:
         f.write(b"\0" * 96)
-        w = _Writer(f, leaf_k)
+        w = _Writer(f, leaf_k, level)
         hdr, bt, hp = w.write_group(data, root=True)
         pos = f.tell()
         if pos % 8:
@@ -318,6 +372,87 @@ class _Reader:
             val = arr
         return name, val
 
+    @staticmethod
+    def parse_filters(data):
+        """Filter pipeline message (versions 1 and 2) -> list of filter ids in pipeline (write) order."""
+        ver, nf = int(data[0]), int(data[1])
+        pos = 8 if ver == 1 else 2
+        ids = []
+        for _ in range(nf):
+            fid = struct.unpack_from("<H", data, pos)[0]
+            pos += 2
+            nlen = 0
+            if ver == 1 or fid >= 256:
+                nlen = struct.unpack_from("<H", data, pos)[0]
+                pos += 2
+            _flags, ncd = struct.unpack_from("<HH", data, pos)
+            pos += 4
+            pos += nlen + ((-nlen % 8) if ver == 1 else 0)
+            pos += 4 * ncd
+            if ver == 1 and ncd % 2:
+                pos += 4
+            ids.append(fid)
+        return ids
+
+    def chunk_leaves(self, bt_addr, rank1, out):
+        """v1 B-tree of raw-data chunks (node type 1): (address, stored bytes, filter mask, offsets) per chunk."""
+        if bytes(self.b[bt_addr:bt_addr + 4]) != b"TREE":
+            raise ValueError("bad chunk B-tree signature")
+        node_type, level, nent = struct.unpack_from("<BBH", self.b, bt_addr + 4)
+        if node_type != 1:
+            raise ValueError("not a raw-data chunk B-tree")
+        key = 8 + 8 * rank1
+        pos = bt_addr + 24
+        for _ in range(nent):
+            size, mask = struct.unpack_from("<II", self.b, pos)
+            offs = struct.unpack_from("<%dQ" % rank1, self.b, pos + 8)
+            child = self.u64(pos + key) + self.base_addr
+            pos += key + 8
+            if level > 0:
+                self.chunk_leaves(child, rank1, out)
+            else:
+                out.append((child, size, mask, offs[:-1]))
+
+    def read_chunked(self, layout, dt, shape, filters):
+        rank1 = int(layout[2])
+        bt = struct.unpack_from("<Q", layout, 3)[0]
+        dims = struct.unpack_from("<%dI" % rank1, layout, 11)
+        cshape = tuple(int(d) for d in dims[:-1])
+        if len(cshape) != len(shape):
+            raise ValueError("chunk rank %d does not match the dataspace rank %d" % (len(cshape), len(shape)))
+        for fid in filters:
+            if fid not in (FILTER_DEFLATE, FILTER_SHUFFLE, FILTER_FLETCHER32):
+                raise NotImplementedError(
+                    "dataset compressed with HDF5 filter %d (%s): only gzip / shuffle / fletcher32 can be decoded without "
+                    "the filter's library; re-export with dd.io.save(path, data, compression='zlib') or compression=None"
+                    % (fid, FILTER_NAMES.get(fid, "unknown")))
+        out = np.zeros(shape, dt)
+        if bt == UNDEF or out.size == 0:
+            return out
+        leaves = []
+        self.chunk_leaves(bt + self.base_addr, rank1, leaves)
+        n_chunk = int(np.prod(cshape))
+        for addr, size, mask, offs in leaves:
+            raw = bytes(self.b[addr:addr + size])
+            for k in range(len(filters) - 1, -1, -1):   # undo the pipeline back to front; a mask bit = filter skipped
+                if mask & (1 << k):
+                    continue
+                fid = filters[k]
+                if fid == FILTER_FLETCHER32:
+                    raw = raw[:-4]
+                elif fid == FILTER_DEFLATE:
+                    raw = zlib.decompress(raw)
+                elif fid == FILTER_SHUFFLE and dt.itemsize > 1:
+                    a = np.frombuffer(raw, np.uint8)
+                    nel = a.size // dt.itemsize
+                    body = a[:nel * dt.itemsize].reshape(dt.itemsize, nel).T.reshape(-1)
+                    raw = body.tobytes() + a[nel * dt.itemsize:].tobytes()
+            chunk = np.frombuffer(raw, dtype=dt, count=n_chunk).reshape(cshape)
+            sel_out = tuple(slice(int(o), min(int(o) + c, s)) for o, c, s in zip(offs, cshape, shape))
+            sel_in = tuple(slice(0, so.stop - so.start) for so in sel_out)
+            out[sel_out] = chunk[sel_in]
+        return out
+
     def read_object(self, hdr_addr, mmap_arrays):
         msgs = self.messages(hdr_addr)
         symtab = [d for t, d in msgs if t == MSG_SYMTAB]
@@ -337,7 +472,10 @@ class _Reader:
             return out
         dt = shape = None
         layout = None
+        filters = []
         for t, d in msgs:
+            if t == MSG_FILTERS:
+                filters = self.parse_filters(d)
             if t == MSG_DATATYPE:
                 dt = self.parse_datatype(d)
             elif t == MSG_DATASPACE:
@@ -359,9 +497,10 @@ class _Reader:
         elif lcls == 0:
             size = struct.unpack_from("<H", layout, 2)[0]
             arr = np.frombuffer(bytes(layout[4:4 + size]), dtype=dt, count=n).reshape(shape)
+        elif lcls == 2:
+            arr = self.read_chunked(layout, dt, shape, filters)
         else:
-            raise NotImplementedError("chunked / compressed datasets (e.g. deepdish's default blosc CArrays) "
-                                      "cannot be read without an HDF5 library")
+            raise NotImplementedError("data layout class %d is not supported" % lcls)
         if not mmap_arrays:
             arr = np.array(arr)
         if dt.kind == "S" and shape == ():
@@ -374,6 +513,7 @@ class _Reader:
 
 
 def load(path, mmap_arrays=False):
-    """Read an HDF5 file written by `save` (or any plain contiguous HDF5 file) into nested dicts."""
+    """Read an HDF5 file written by `save`, or a contiguous / chunked (gzip, shuffle) HDF5 file written by an HDF5
+    library, into nested dicts."""
     buf = np.memmap(path, dtype=np.uint8, mode="r")
     return _Reader(buf).root(mmap_arrays)

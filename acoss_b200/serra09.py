@@ -101,41 +101,54 @@ class Serra09(CoverAlgorithm):
     def load_features_batch(self, ids, batch=256):
         """load_features for many songs at once, the x40 aggregation and the global chroma done on
         the device (acoss_aggregate_songs).  Same results as load_features, bit
-        for bit; songs that are already prepared or cached are skipped."""
+        for bit; songs that are already prepared or cached are skipped.  Feature files are read one
+        batch at a time and only the fields this plugin uses are kept; a batch is split by dtype so that
+        float32 songs are aggregated in float32 as numpy would; factors beyond the kernel's block size
+        take the host path."""
         todo = [int(i) for i in np.unique(np.asarray(ids, dtype=np.int64)) if int(i) not in self.all_feats]
-        raw = []
-        for i in todo:
-            feats = CoverAlgorithm.load_features(self, i)
-            if 'gchroma' in feats and 'chroma' in feats:
-                self.load_features(i)
-            else:
-                raw.append((i, feats))
-        if not raw:
+        if not todo:
             return
-        if self._feat_ctx is None:
-            self._feat_ctx = _native.Context(self.device)
-        ctx = self._feat_ctx
-        for b0 in range(0, len(raw), batch):
-            part = raw[b0:b0 + batch]
-            chromas = [np.asarray(f[self.chroma_type]) for _, f in part]
-            for c in chromas:
-                if c.shape[1] not in [12, 24, 36]:   # global_chroma's check, Serra09.py:25-26
+        if self.downsample_fac > 64:   # kFeatMaxFac of csrc/kernels_feat.cuh
+            for i in todo:
+                self.load_features(i)
+            return
+        for b0 in range(0, len(todo), batch):
+            part = []
+            for i in todo[b0:b0 + batch]:
+                feats = CoverAlgorithm.load_features(self, i)
+                if 'gchroma' in feats and 'chroma' in feats:
+                    self.load_features(i)
+                    continue
+                chroma = np.asarray(feats[self.chroma_type])
+                if chroma.shape[1] not in [12, 24, 36]:   # global_chroma's check, Serra09.py:25-26
                     raise IOError("Wrong axis for the input chroma array. Expected shape '(frame_size, bin_size)'")
-            agg, g = ctx.aggregate_songs(chromas, fac=self.downsample_fac, aggregate="median", want_gchroma=True)
-            mf = [None] * len(part)
-            have = [k for k, (_, f) in enumerate(part) if self.do_mfcc and 'mfcc_htk' in f]
-            if have:
-                res = ctx.aggregate_songs([np.asarray(part[k][1]['mfcc_htk']) for k in have], fac=self.downsample_fac,
-                                          aggregate="mean", layout="bins_x_frames", zero_nonfinite=True)
-                for k, r in zip(have, res):
-                    mf[k] = r
-            for k, (i, _) in enumerate(part):
+                mfcc = np.asarray(feats['mfcc_htk']) if (self.do_mfcc and 'mfcc_htk' in feats) else None
+                part.append((i, chroma, mfcc))
+            if not part:
+                continue
+            if self._feat_ctx is None:
+                self._feat_ctx = _native.Context(self.device)
+            ctx = self._feat_ctx
+            agg, g, mf = [None] * len(part), [None] * len(part), [None] * len(part)
+            for dt in sorted({c.dtype for _, c, _ in part}, key=str):
+                sel = [k for k, (_, c, _) in enumerate(part) if c.dtype == dt]
+                a, gg = ctx.aggregate_songs([part[k][1] for k in sel], fac=self.downsample_fac, aggregate="median",
+                                            want_gchroma=True)
+                for q, k in enumerate(sel):
+                    agg[k], g[k] = a[q], gg[q].copy()
+            for dt in sorted({m.dtype for _, _, m in part if m is not None}, key=str):
+                sel = [k for k, (_, _, m) in enumerate(part) if m is not None and m.dtype == dt]
+                res = ctx.aggregate_songs([part[k][2] for k in sel], fac=self.downsample_fac, aggregate="mean",
+                                          layout="bins_x_frames", zero_nonfinite=True)
+                for q, k in enumerate(sel):
+                    mf[k] = res[q]
+            for k, (i, _, _) in enumerate(part):
                 chroma, mfcc = np.asfortranarray(agg[k]), mf[k]
                 if mfcc is not None:
                     N = min(chroma.shape[1], mfcc.shape[1])      # Serra09.py:111-114
                     chroma = chroma[:, 0:N]
                     mfcc = np.asfortranarray(mfcc)[:, 0:N]
-                self.all_feats[i] = {'gchroma': g[k].copy(), 'chroma': chroma, 'mfcc': mfcc, 'ssms': None}
+                self.all_feats[i] = {'gchroma': g[k], 'chroma': chroma, 'mfcc': mfcc, 'ssms': None}
 
     # ------------------------------------------------------------------ device arena
     def _context_for(self, kind, song_ids):

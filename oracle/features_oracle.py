@@ -6,13 +6,58 @@ librosa.util.sync(data, np.arange(0, n, fac), aggregate=np.median | np.mean) (Se
 
 Parity pinning: global_chroma is the reference's own three lines and is checked against the
 reference module's arithmetic by construction (np.sum(axis=0) / np.max).  librosa (pinned 0.6.3 in
-requirements.txt) is NOT under /root/reference and not installed here, so the slicing convention of
-util.sync -- slice k = frames [idx[k], idx[k+1]) with the last slice running to n, and the
-aggregate applied along the time axis -- is restated from its published documentation:
-PARITY UNPINNED for that convention; the aggregates themselves are numpy's own np.median/np.mean.
+requirements.txt) is a third-party dependency that is NOT under /root/reference, is not installed here
+and cannot be fetched (no network), so its source lines cannot be quoted; the algorithm of
+librosa.util.sync in the 0.6 series is restated below step by step (sync_slices):
+  sync(data, idx, aggregate, pad=True, axis=-1)
+    -> slices = util.index_to_slice(np.asarray(idx), 0, data.shape[axis], pad=True)
+  index_to_slice(idx, idx_min, idx_max, step=None, pad=True)
+    -> idx_fixed = util.fix_frames(idx, idx_min, idx_max, pad=pad)
+       [slice(start, end, step) for (start, end) in zip(idx_fixed, idx_fixed[1:])]
+  fix_frames(frames, x_min=0, x_max=None, pad=True)
+    -> clip frames to [x_min, x_max]; with pad, prepend x_min and x_max to the list;
+       keep x_min <= frames <= x_max; return np.unique(frames)   (sorted, duplicates removed)
+  and every slice is reduced with aggregate(data[..., slice], axis=axis).
+With idx = np.arange(0, n, fac) (Serra09.py:104,110) the boundaries are unique([0, n, 0, fac, 2 fac, ...]) =
+[0, fac, ..., fac * floor((n-1)/fac), n]: ceil(n / fac) slices, the last one shorter when fac does not divide n,
+exactly n / fac slices when it does (the padded boundary n coincides with no extra slice), one slice [0, n) when
+n <= fac.  `sync` (the closed form used by the kernels' tests) is checked against `sync_slices` in
+tests/test_features.py for those edge cases.  PARITY UNPINNED against librosa itself: nothing here can execute it.
 Only tests/ and bench.py's cpu_baseline may import this module.
 """
 import numpy as np
+
+
+def fix_frames(frames, x_min=0, x_max=None, pad=True):
+    """librosa.util.fix_frames (0.6 series), restated."""
+    frames = np.asarray(frames)
+    if np.any(frames < 0):
+        raise ValueError("Negative frame index detected")
+    if pad and (x_min is not None or x_max is not None):
+        frames = np.clip(frames, x_min, x_max)
+    if pad:
+        pad_data = []
+        if x_min is not None:
+            pad_data.append(x_min)
+        if x_max is not None:
+            pad_data.append(x_max)
+        frames = np.concatenate((np.asarray(pad_data, dtype=frames.dtype), frames))
+    if x_min is not None:
+        frames = frames[frames >= x_min]
+    if x_max is not None:
+        frames = frames[frames <= x_max]
+    return np.unique(frames).astype(int)
+
+
+def sync_slices(data, idx, aggregate):
+    """librosa.util.sync(data, idx, aggregate=aggregate) for a (d, n) array through the restated index_to_slice /
+    fix_frames: the literal form."""
+    n = data.shape[-1]
+    b = fix_frames(np.asarray(idx), 0, n, pad=True)
+    out = np.empty((data.shape[0], len(b) - 1), dtype=data.dtype, order="F")
+    for k, (s, e) in enumerate(zip(b, b[1:])):
+        out[:, k] = aggregate(data[:, s:e], axis=-1)
+    return out
 
 
 def global_chroma(chroma):

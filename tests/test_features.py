@@ -15,6 +15,21 @@ def _songs(rng, dtype, n_list, bins=12):
     return out
 
 
+def test_sync_closed_form_equals_restated_librosa_slicing():
+    """librosa.util.sync's slicing (fix_frames + index_to_slice, restated in oracle/features_oracle.py) against the
+    closed form the kernels are tested with, on the edge cases: n a multiple of fac, n < fac, n = fac, n = fac + 1."""
+    rng = np.random.default_rng(5)
+    for n in (1, 7, 39, 40, 41, 79, 80, 81, 120, 333, 4000):
+        a = rng.random((12, n))
+        for agg in (np.median, np.mean):
+            lit = fo.sync_slices(a, np.arange(0, n, 40), agg)
+            assert lit.shape[1] == -(-n // 40)
+            assert np.array_equal(lit, fo.sync(a, 40, agg)), (n, agg.__name__)
+    assert list(fo.fix_frames(np.arange(0, 80, 40), 0, 80)) == [0, 40, 80]
+    assert list(fo.fix_frames(np.arange(0, 30, 40), 0, 30)) == [0, 30]
+    assert list(fo.fix_frames(np.arange(0, 81, 40), 0, 81)) == [0, 40, 80, 81]
+
+
 def test_oracle_sync_matches_numpy_semantics():
     rng = np.random.default_rng(0)
     a = rng.random((12, 95)).astype(np.float32)

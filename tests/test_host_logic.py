@@ -174,3 +174,36 @@ def test_serra09_load_features_from_files(tmp_path):
     L = int(np.ceil((400 + 74) / 40))
     assert f["chroma"].shape == (12, L) and f["mfcc"].shape == (13, L) and f["gchroma"].shape == (12,)
     assert alg.cliques == {"c0": {2}}
+
+
+def test_hdf5_chunked_gzip_shuffle_roundtrip_and_filters(tmp_path):
+    """Chunked datasets with the shuffle + gzip filters (what deepdish / PyTables write with compression='zlib'):
+    several chunks, ragged last chunk, 1-D / 2-D / 3-D, every numeric kind; the filter-pipeline parser on version-1 and
+    version-2 messages; blosc is refused with an instruction to re-export.  No HDF5 library exists here, so the file is
+    assembled by hdf5io's own writer from the format specification (interop unpinned, see hdf5io's docstring)."""
+    import struct
+    rng = np.random.default_rng(0)
+    d = {"hpcp": rng.random((30011, 12)).astype(np.float32), "crema": rng.random((7001, 12)),
+         "mfcc_htk": (rng.standard_normal((13, 5000)) * 30).astype(np.float32), "ids": np.arange(300000, dtype=np.int64),
+         "cube": rng.integers(0, 255, size=(70, 50, 40)).astype(np.uint8), "label": "W_123", "track_id": "P_1",
+         "madmom_features": {"onsets": rng.random(77), "tempos": rng.random((3, 2)), "empty": np.zeros((0, 2))}}
+    path = str(tmp_path / "song.h5")
+    hdf5io.save(path, d, compression="zlib")
+    plain = str(tmp_path / "plain.h5")
+    hdf5io.save(plain, d)
+    assert os.path.getsize(path) < os.path.getsize(plain)
+    out = hdf5io.load(path)
+    for k in ("hpcp", "crema", "mfcc_htk", "ids", "cube"):
+        assert out[k].dtype == d[k].dtype and np.array_equal(out[k], d[k]), k
+    assert out["label"] == "W_123" and np.array_equal(out["madmom_features"]["tempos"], d["madmom_features"]["tempos"])
+    assert out["madmom_features"]["empty"].shape == (0, 2)
+    # filter pipeline messages: version 1 (padded names) and version 2 (no name for ids < 256)
+    v1 = struct.pack("<BB6x", 1, 2) + struct.pack("<HHHH", 2, 8, 0, 1) + b"shuffle\0" + struct.pack("<II", 4, 0) \
+        + struct.pack("<HHHH", 1, 8, 1, 1) + b"deflate\0" + struct.pack("<II", 5, 0)
+    v2 = struct.pack("<BB", 2, 2) + struct.pack("<HHH", 2, 0, 1) + struct.pack("<I", 4) + struct.pack("<HHH", 1, 1, 1) + struct.pack("<I", 5)
+    assert hdf5io._Reader.parse_filters(v1) == [2, 1] and hdf5io._Reader.parse_filters(v2) == [2, 1]
+    blosc = struct.pack("<BB", 2, 1) + struct.pack("<HHHH", 32001, 6, 0, 0) + b"blosc\0"
+    assert hdf5io._Reader.parse_filters(blosc) == [32001]
+    r = hdf5io._Reader(np.memmap(path, dtype=np.uint8, mode="r"))
+    with pytest.raises(NotImplementedError, match="blosc.*re-export"):
+        r.read_chunked(struct.pack("<BBB", 3, 2, 2) + struct.pack("<Q", 0) + struct.pack("<II", 4, 4), np.dtype("f4"), (8,), [32001])
