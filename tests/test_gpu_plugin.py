@@ -111,3 +111,32 @@ def test_raw_features_are_aggregated_on_the_device(tmp_path, monkeypatch):
         assert np.array_equal(sa[k], sb[k]), k
     a.close()
     b.close()
+
+
+def test_chen_fusion_plugin_vs_oracle(tmp_path, monkeypatch):
+    """ChenFusion.similarity (ChenFusion.py:57-67): blocked OTI + Euclidean CSM of the one-step "stack" + row-only kNN +
+    qmax / dmax on zeroed tables, un-normalised; then normalize_by_length (ChenFusion.py:69-79)."""
+    from acoss_b200.chen_fusion import ChenFusion
+    from oracle import crp_oracle, dp
+    songs, labels = synth.make_song_set("covers80", seed=71, n_songs=10, length_range=(100, 420))
+    monkeypatch.chdir(tmp_path)
+    alg = ChenFusion(songs=songs, labels=labels, shortname="chen", do_memmaps=True)
+    alg.all_pairwise(symmetric=True)
+    n = len(songs)
+    for i in range(n):
+        for j in range(i + 1, n):
+            _, _, S = crp_oracle.crp_pair(songs[i]["chroma"].astype(np.float64), songs[j]["chroma"].astype(np.float64),
+                                          songs[i]["gchroma"], songs[j]["gchroma"], 1, 0.095, want_S=True)
+            B = crp_oracle.knn_mask(S, 0.095)
+            assert alg.Ds["qmax"][i, j] == np.float32(dp.qmax_only(B)) and alg.Ds["dmax"][i, j] == np.float32(dp.dmax_clean(B))
+            assert alg.Ds["qmax"][j, i] == alg.Ds["qmax"][i, j]
+    q = np.array(alg.Ds["qmax"])
+    alg.normalize_by_length()
+    L = np.array([s["chroma"].shape[1] for s in songs], np.float64)
+    with np.errstate(divide="ignore"):
+        assert np.array_equal(np.asarray(alg.Ds["qmax"]), (np.sqrt(L)[None, :] / q.astype(np.float64)).astype(np.float32))
+    with pytest.raises(NotImplementedError):
+        alg.do_late_fusion()
+    with pytest.raises(NotImplementedError):
+        ChenFusion(songs=songs, labels=labels, tau=2, do_memmaps=False)
+    alg.close()
