@@ -60,6 +60,9 @@ SIGNATURES = {
     "acoss_reset_counters": (None, [ctypes.c_void_p]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
+    "acoss_upload_aux_songs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int32]),
+    "acoss_snf_pairs": (ctypes.c_int, [ctypes.c_void_p, _c_i32p, ctypes.c_int64, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
+                                       ctypes.c_uint32, _c_f32p, _c_f32p, _c_i32p, _c_i32p, _c_f64p, _c_i64p, _c_u32p, _c_i64p]),
     "acoss_dp_packed_static": (ctypes.c_int, [ctypes.c_int32, ctypes.c_void_p, _c_i64p, _c_i32p, _c_i32p, ctypes.c_int32,
                                               ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]),
     "acoss_debug_sweep7_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
@@ -187,6 +190,45 @@ class Context:
                                          _ptr(lengths, _c_i32p), len(lengths), self.bins,
                                          ctypes.cast(ctypes.c_void_p(int(gchroma_ptr)), _c_f64p) if gchroma_ptr else None)
         self._check(rc, "acoss_upload_songs")
+
+    def upload_aux(self, frames):
+        """Second feature arena of the songs already uploaded (same offsets / lengths), e.g. mfcc: (total_frames, bins)."""
+        frames = np.ascontiguousarray(frames)
+        if frames.dtype not in (np.float32, np.float64):
+            raise TypeError("frames must be float32 or float64")
+        rc = self.lib.acoss_upload_aux_songs(self._h, frames.ctypes.data_as(ctypes.c_void_p),
+                                             F32 if frames.dtype == np.float32 else F64, int(frames.shape[1]))
+        self._check(rc, "acoss_upload_aux_songs")
+
+    def snf_pairs(self, pairs, m=9, kappa=0.095, niters=3, flags=0, want_fused=False, want_crp=False):
+        """EarlySNF's fusion + tail for (P, 2) pairs: dict with qmax_raw, dmax_raw, oti, shape [, fused: list of (M, N)
+        float64 = MINUS the fused cross block, crp: list of uint8 (M, N)]."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        P = pairs.shape[0]
+        q, d = np.zeros(P, np.float32), np.zeros(P, np.float32)
+        oti, shape = np.zeros(P, np.int32), np.zeros((P, 2), np.int32)
+        L = self.lengths
+        Mi = np.maximum(L[pairs[:, 0]].astype(np.int64) - m + 1, 0)
+        Nj = np.maximum(L[pairs[:, 1]].astype(np.int64) - m + 1, 0)
+        fbuf = foff = cbuf = coff = None
+        if want_fused:
+            foff = np.concatenate(([0], np.cumsum(Mi * Nj)[:-1])).astype(np.int64)
+            fbuf = np.zeros(max(int((Mi * Nj).sum()), 1), np.float64)
+        if want_crp:
+            words = Mi * ((Nj + 31) // 32)
+            coff = np.concatenate(([0], np.cumsum(words)[:-1])).astype(np.int64)
+            cbuf = np.zeros(max(int(words.sum()), 1), np.uint32)
+        rc = self.lib.acoss_snf_pairs(self._h, _ptr(pairs, _c_i32p), P, int(m), float(kappa), int(niters), int(flags),
+                                      _ptr(q, _c_f32p), _ptr(d, _c_f32p), _ptr(oti, _c_i32p), _ptr(shape, _c_i32p),
+                                      _ptr(fbuf, _c_f64p), _ptr(foff, _c_i64p), _ptr(cbuf, _c_u32p), _ptr(coff, _c_i64p))
+        self._check(rc, "acoss_snf_pairs")
+        out = {"qmax_raw": q, "dmax_raw": d, "oti": oti, "shape": shape}
+        if want_fused:
+            out["fused"] = [fbuf[o:o + a * b].reshape(int(a), int(b)) for o, a, b in zip(foff, Mi, Nj)]
+        if want_crp:
+            out["crp"] = [unpack_bits(cbuf[o:o + a * ((b + 31) // 32)].reshape(int(a), int((b + 31) // 32)), int(b))
+                          if a > 0 and b > 0 else np.zeros((int(a), int(b)), np.uint8) for o, a, b in zip(coff, Mi, Nj)]
+        return out
 
     # ------------------------------------------------------------------ scoring
     def serra09_pairs(self, pairs, m=9, kappa=0.095, flags=0, want_crp=False, want_sw=False):

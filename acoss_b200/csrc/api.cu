@@ -824,7 +824,8 @@ int acoss_destroy(acoss_ctx* c) {
     DevBuf* bufs[] = {&c->frames, &c->norms, &c->offs, &c->gchroma, &c->pairs, &c->items, &c->counters,
                       &c->seps, &c->crp, &c->bnd, &c->qout, &c->dout, &c->swout, &c->otiout, &c->gscratch,
                       &c->dense_in, &c->dense_desc, &c->dense_starts,
-                      &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb, &c->eval_D, &c->tmat};
+                      &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb, &c->eval_D, &c->tmat,
+                      &c->frames2, &c->snf_desc, &c->snf_mats, &c->snf_md, &c->snf_sidx, &c->snf_sval};
     for (DevBuf* b : bufs) b->release();
     c->h_stage.release();
     for (int i = 0; i < 5; ++i)
@@ -887,6 +888,12 @@ int acoss_upload_songs(acoss_ctx* c, const void* frames, int dtype, const int64_
         CU(cudaMemcpyAsync(c->gchroma.p, gchroma, (size_t)n_songs * bins * sizeof(double), cudaMemcpyDefault, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
+    c->h_gchroma.clear();
+    c->bins2 = 0;   // a new song set invalidates the auxiliary arena
+    if (gchroma) {
+        c->h_gchroma.resize((size_t)n_songs * bins);
+        CU(cudaMemcpy(c->h_gchroma.data(), c->gchroma.p, (size_t)n_songs * bins * sizeof(double), cudaMemcpyDeviceToHost));
+    }
     return ACOSS_OK;
 }
 
@@ -999,12 +1006,15 @@ int acoss_dp_packed(acoss_ctx* c, const uint32_t* crp, const int64_t* crp_offset
     return ACOSS_OK;
 }
 
-int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* csm_offsets, const int32_t* rows,
-                      const int32_t* cols, int32_t B, double kappa, uint32_t flags, float* out, uint32_t* crp_out,
-                      const int64_t* crp_offsets) {
+}  // extern "C"
+
+// csm == nullptr: the matrices are already in c->dense_in (acoss_align_dense_resident)
+static int align_dense_impl(acoss_ctx* c, const void* csm, int dtype, const int64_t* csm_offsets, const int32_t* rows,
+                            const int32_t* cols, int32_t B, double kappa, uint32_t flags, float* out, uint32_t* crp_out,
+                            const int64_t* crp_offsets) {
     int rc = check_ctx(c);
     if (rc) return rc;
-    if (B < 0 || (B > 0 && (!csm || !csm_offsets || !rows || !cols || !out))) return fail(ACOSS_ERR_ARG, "null input");
+    if (B < 0 || (B > 0 && (!rows || !cols || !out))) return fail(ACOSS_ERR_ARG, "null input");
     if (dtype != ACOSS_F32 && dtype != ACOSS_F64) return fail(ACOSS_ERR_ARG, "unknown dtype %d", dtype);
     if (!(kappa > 0.0)) return fail(ACOSS_ERR_ARG, "kappa must be > 0");
     if (crp_out && !crp_offsets) return fail(ACOSS_ERR_ARG, "crp_out needs crp_offsets");
@@ -1046,7 +1056,8 @@ int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* c
         crp_total += (int64_t)d.rows * d.wp;
         lines += (int64_t)d.rows + d.cols;
     }
-    CU(c->dense_in.reserve((size_t)el_total * esz));
+    if (csm) CU(c->dense_in.reserve((size_t)el_total * esz));
+    else if (c->dense_in.cap < (size_t)el_total * esz) return fail(ACOSS_ERR_STATE, "resident dense input is smaller than the shapes say");
     CU(c->dense_desc.reserve((size_t)B * sizeof(DenseDesc)));
     CU(c->dense_starts.reserve((size_t)2 * B * sizeof(int64_t)));
     CU(c->pairs.reserve((size_t)B * sizeof(PairWork)));
@@ -1057,7 +1068,7 @@ int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* c
     CU(c->dout.reserve((size_t)B * sizeof(float)));
     CU(c->swout.reserve((size_t)B * sizeof(float)));
     CU(c->items.reserve((size_t)B * sizeof(uint32_t)));
-    for (int b = 0; b < B; ++b)
+    for (int b = 0; b < B && csm; ++b)
         CU(cudaMemcpyAsync(c->dense_in.as<char>() + D[b].csm_off * esz,
                            reinterpret_cast<const char*>(csm) + csm_offsets[b] * esz,
                            (size_t)D[b].rows * D[b].cols * esz, cudaMemcpyHostToDevice, c->stream));
@@ -1112,6 +1123,20 @@ int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* c
             memcpy(crp_out + crp_offsets[b], c->h_crp.data() + D[b].crp_off, (size_t)D[b].rows * D[b].wp * sizeof(uint32_t));
     }
     return ACOSS_OK;
+}
+
+int acoss_align_dense_resident(acoss_ctx* c, int dtype, const int32_t* rows, const int32_t* cols, int32_t B, double kappa,
+                               uint32_t flags, float* out, uint32_t* crp_out, const int64_t* crp_offsets) {
+    return align_dense_impl(c, nullptr, dtype, nullptr, rows, cols, B, kappa, flags, out, crp_out, crp_offsets);
+}
+
+extern "C" {
+
+int acoss_align_dense(acoss_ctx* c, const void* csm, int dtype, const int64_t* csm_offsets, const int32_t* rows,
+                      const int32_t* cols, int32_t B, double kappa, uint32_t flags, float* out, uint32_t* crp_out,
+                      const int64_t* crp_offsets) {
+    if (B > 0 && (!csm || !csm_offsets)) return fail(ACOSS_ERR_ARG, "null input");
+    return align_dense_impl(c, csm, dtype, csm_offsets, rows, cols, B, kappa, flags, out, crp_out, crp_offsets);
 }
 
 static int dp_unpacked(acoss_ctx* c, const uint8_t* S, int32_t rows, int32_t cols, uint32_t flags, float out[3]) {

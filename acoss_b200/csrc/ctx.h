@@ -100,6 +100,11 @@ struct acoss_ctx {
     int n_songs = 0, bins = 0;
     int64_t total_frames = 0;
     bool has_gchroma = false;
+    // second feature arena of the same songs (e.g. mfcc beside chroma) and a host copy of gchroma: the SNF front end
+    DevBuf frames2;
+    int bins2 = 0;
+    std::vector<double> h_gchroma;
+    DevBuf snf_desc, snf_mats, snf_md, snf_sidx, snf_sval;
     // per-chunk scratch
     DevBuf pairs, items, counters, seps, crp, bnd, qout, dout, swout, otiout, gscratch;
     DevBuf dense_in, dense_desc, dense_starts;
@@ -138,3 +143,7 @@ struct acoss_ctx {
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
+// api.cu: the EarlySNF tail (binarise + DPs) over B float64 / float32 matrices ALREADY in ctx->dense_in, matrix b at the
+// running sum of rows x cols elements; same outputs as acoss_align_dense.
+int acoss_align_dense_resident(acoss_ctx* c, int dtype, const int32_t* rows, const int32_t* cols, int32_t B, double kappa,
+                               uint32_t flags, float* out, uint32_t* crp_out, const int64_t* crp_offsets);

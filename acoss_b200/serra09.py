@@ -179,6 +179,7 @@ class Serra09(CoverAlgorithm):
             packed = _native.pack_songs(songs, pinned=True)   # host arena, page-locked when a GPU is present
             self._packed[kind] = (need, packed)
         ctx.upload(*packed)
+        self._upload_gen = getattr(self, '_upload_gen', 0) + 1   # (EarlySNF re-attaches its second arena after an upload)
         slot = -np.ones(self.N, dtype=np.int64)
         slot[need] = np.arange(len(need))
         self._ctx[kind] = (ctx, slot)

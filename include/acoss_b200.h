@@ -25,6 +25,8 @@
  *                           the Cython FFI itself (pySeqAlign.pyx:7-23): S uint8 [M*N],
  *                           same argument order and return value; the caller's float D
  *                           table is not needed (and not filled)
+ *   acoss_snf_pairs         EarlySNF.similarity's fusion step (EarlySNF.py:44-57, 85-90;
+ *                           SimilarityFusion.py:50-177, 202-277) + its binarise / qmax / dmax tail
  *   acoss_dp_packed         batched qmax/dmax/sw over caller-supplied bit-packed CRPs
  *   acoss_aggregate_songs   Serra09.load_features' block aggregation + global_chroma
  *                           (benchmarking/Serra09.py:24-28, 96-114)
@@ -118,6 +120,22 @@ int acoss_align_dense(acoss_ctx* ctx, const void* csm, int dtype, const int64_t*
                       const int32_t* rows, const int32_t* cols, int32_t B,
                       double kappa, uint32_t flags, float* out,
                       uint32_t* crp_out, const int64_t* crp_offsets);
+
+/*
+ * Similarity-network-fusion front end of EarlySNF (benchmarking/EarlySNF.py:44-57, 85-90 with
+ * benchmarking/SimilarityFusion.py:50-177, 202-277: get_WCSMSSM, get_P, get_S, snf_ws(niters, reg_diag=True)),
+ * followed by the EarlySNF tail (csm_to_binary_mutual -> qmax / dmax on one table).  Two feature kinds are fused:
+ * the arena of acoss_upload_songs (kind 0, rolled by the OTI of the pair unless ACOSS_FLAG_NO_OTI) and a second
+ * arena of the SAME songs (same offsets and lengths, e.g. the 13-bin mfcc sequence) uploaded with
+ * acoss_upload_aux_songs; the reference's second kind, the scattering-transform SSMs, needs kymatio and is out of
+ * scope.  K = int(kappa (M + N)) neighbours, float64 throughout.  Limits: M + N <= 2048, K <= 256.
+ * Outputs per pair: raw qmax / dmax maxima, oti, shape (M, N); optionally minus-the-fused cross block
+ * (fused_out + fused_offsets[p], M x N float64, row-major: the matrix the reference binarises) and its packed CRP.
+ */
+int acoss_upload_aux_songs(acoss_ctx* ctx, const void* frames, int dtype, int32_t bins);
+int acoss_snf_pairs(acoss_ctx* ctx, const int32_t* pairs, int64_t P, int32_t m, double kappa, int32_t niters,
+                    uint32_t flags, float* qmax_raw, float* dmax_raw, int32_t* oti_out, int32_t* shape_out,
+                    double* fused_out, const int64_t* fused_offsets, uint32_t* crp_out, const int64_t* crp_offsets);
 
 /*
  * Batched DPs over caller-supplied packed CRPs (same packing as the debug dump).
