@@ -48,6 +48,8 @@ CONFIGS = {
     # name: (synth shape, songs, seed, description)
     "whatisacover": ("whatisacover", 10000, 10000, "whatisacover-subset-shaped synthetic HPCP (BASELINE configs[1])"),
     "benchmark": ("benchmark", 15000, 15000, "Da-TACOS benchmark-subset-shaped synthetic HPCP (BASELINE configs[2]: 1000 cliques x 13 + 2000 singletons)"),
+    "earlysnf": ("benchmark", 2000, 15000, "EarlySNF fused-matrix alignment over benchmark-subset shapes (BASELINE configs[3]): chroma + mfcc kernels "
+                                           "fused by similarity network fusion, fused cross block -> mutual kNN -> Qmax / Dmax"),
 }
 TILE = 32  # song tile edge of the bench's pair tiles (1024 pairs per off-diagonal tile)
 
@@ -354,6 +356,126 @@ def run_b200(args, rank, world, local):
     return finish_b200(locals())
 
 
+def add_mfcc(songs, seed=13):
+    """Synthetic 13-bin mfcc-like sequences of the songs' lengths (smoothed random walk + noise)."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for sgs in songs:
+        L = sgs["chroma"].shape[1]
+        fr = rng.normal(size=(L, 13)).cumsum(axis=0).astype(np.float32) * 0.1 + rng.normal(size=(L, 13)).astype(np.float32)
+        out.append({"chroma": sgs["chroma"], "gchroma": sgs["gchroma"], "mfcc": np.ascontiguousarray(fr.T)})
+    return out
+
+
+def _cpu_snf_chunk(chunk):
+    from oracle import snf_oracle
+    out = []
+    for i, j in chunk:
+        Si, Sj = _CPU_SONGS[int(i)], _CPU_SONGS[int(j)]
+        r = snf_oracle.early_snf_pair(Si["chroma"].astype(np.float64), Sj["chroma"].astype(np.float64), Si["gchroma"], Sj["gchroma"],
+                                      Si["mfcc"].astype(np.float64), Sj["mfcc"].astype(np.float64), M_WIN, KAPPA, 3)
+        out.append(r["qmax_raw"])
+    return out
+
+
+def run_earlysnf(args, rank, world, local):
+    """--config earlysnf (BASELINE configs[3]): a step = acoss_snf_pairs over a seeded batch of pairs (fusion of the chroma
+    and mfcc kernels + the binarise / Qmax / Dmax tail), the step's pairs split evenly over the ranks; songs resident."""
+    import multiprocessing as mp
+    import torch
+    import torch.distributed as dist
+    from acoss_b200 import _native, parallel
+    global _CPU_SONGS
+    songs, labels = make_workload(args)
+    songs = add_mfcc(songs)
+    N = len(songs)
+    lengths = np.array([s["chroma"].shape[1] for s in songs])
+    per_step = args.pairs_per_step if args.pairs_per_step != 1200000 else 384
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        n = args.cpu_pairs or 12 * cores   # ~0.8 s per pair and core
+        _CPU_SONGS = songs
+        pairs = step_pairs(N, n, 10_000, 0, 1)
+        with mp.get_context("fork").Pool(cores) as pool:
+            pool.map(_cpu_snf_chunk, [pairs[:1]] * cores)
+            t0 = time.perf_counter()
+            pool.map(_cpu_snf_chunk, [pairs[k:k + 1] for k in range(n)], chunksize=1)
+            secs = time.perf_counter() - t0
+        cpu_base = {"value": n / secs, "unit": "pairs/s", "cores": cores, "kind": "port", "seconds": secs,
+                    "sample": "%d uniformly drawn pairs; oracle/snf_oracle.py (numpy restatement of SimilarityFusion.py, pinned by the "
+                              "reference's own output) + the reference's SequenceAlignment.c; %d processes" % (n, cores)}
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        parallel.init_distributed()
+    ctx = _native.Context(local)
+    ctx.upload_songs(songs)
+    ctx.upload_aux(np.concatenate([s["mfcc"].T for s in songs], axis=0))
+
+    def my_pairs(step):
+        allp = step_pairs(N, per_step, step, 0, 1)
+        return allp[rank::world]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for s in range(args.warmup):
+        ctx.snf_pairs(my_pairs(s), m=M_WIN, kappa=KAPPA, niters=3)
+    batches = [my_pairs(args.warmup + s) for s in range(args.steps)]
+    sampler = ClockSampler(local)
+    ctx.reset_counters()
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    for b in batches:
+        ctx.snf_pairs(b, m=M_WIN, kappa=KAPPA, niters=3)
+    barrier()
+    dt = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    # algorithmic flops of the cross diffusion: per pair, kind and iteration two products of K n^2 multiply-adds
+    flops = 0.0
+    for b in batches:
+        n = (lengths[b[:, 0]] - M_WIN + 1 + lengths[b[:, 1]] - M_WIN + 1).astype(np.float64)
+        flops += float((2 * 2 * 3 * 2.0 * np.floor(KAPPA * n) * n * n).sum())
+    tot = torch.tensor([dt, flops, float(ctx.kernel_launches())], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = tot[:1].clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        tot[0] = tmax[0]
+    dt, flops, launches = [float(x) for x in tot]
+    if rank == 0:
+        sm_max = (clocks or {}).get("sm_max_mhz") or 1965.0
+        peak = N_SM * FP64_LANES_PER_SM * 2 * sm_max * 1e6 / 1e12
+        total_pairs = per_step * args.steps
+        line = {"metric": "song_pairs_per_sec", "value": total_pairs / dt, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "%s: %d songs with synthetic 13-bin mfcc, %d pairs per step, m = %d, kappa = %.3f, 3 fusion iterations"
+                                       % (CONFIGS[args.config][3], N, per_step, M_WIN, KAPPA), "songs": N, "pairs_per_step_total": per_step,
+                           "l2_policy": "inputs larger than L2 (about 32 MB of (M+N)^2 float64 matrices per pair, hundreds of pairs per call)"},
+                "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": {"value": total_pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": int(per_step * 8), "d2h_bytes_per_step": int(per_step * 24),
+                        "note": "acoss_snf_pairs takes the pair list from the host and returns the scores to the host inside the timed call; the "
+                                "songs are resident (uploaded once)"},
+                "roofline": {"bound": "tensor", "achieved": flops / dt / 1e12, "peak": peak, "unit": "TFLOP/s", "frac": flops / dt / 1e12 / peak,
+                             "traffic": None, "kernel": "k_snf_xst + k_snf_sy (cross diffusion S (P S^T), float64 SIMT gather / axpy)",
+                             "note": "algorithmic flops = 2 kinds x 3 iterations x 2 products x 2 K n^2 per pair over the WHOLE step time (all "
+                                     "kernels of the call); FP64 peak as for the main path"}}
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def default_plugin_rate(args, songs, labels, local, n_pairs=100000):
     """The reference's default call computes chroma AND mfcc scores (Serra09.py:94,177-184): pairs/s of
     Serra09(do_mfcc=True).similarity on synthetic 13-bin mfcc-like features of the same lengths (N = 1 only)."""
@@ -515,6 +637,9 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.config == "earlysnf":
+        run_earlysnf(args, rank, world, local)
         return
     run_b200(args, rank, world, local)
     if world > 1:
