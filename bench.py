@@ -48,6 +48,8 @@ CONFIGS = {
     # name: (synth shape, songs, seed, description)
     "whatisacover": ("whatisacover", 10000, 10000, "whatisacover-subset-shaped synthetic HPCP (BASELINE configs[1])"),
     "benchmark": ("benchmark", 15000, 15000, "Da-TACOS benchmark-subset-shaped synthetic HPCP (BASELINE configs[2]: 1000 cliques x 13 + 2000 singletons)"),
+    "stress": ("covers80", 96, 4096, "long-song stress (BASELINE configs[4]): 4096-frame HPCP songs plus a mixed 1024..4096 set, m = 20, "
+                                     "variable-length batching"),
     "earlysnf": ("benchmark", 2000, 15000, "EarlySNF fused-matrix alignment over benchmark-subset shapes (BASELINE configs[3]): chroma + mfcc kernels "
                                            "fused by similarity network fusion, fused cross block -> mutual kNN -> Qmax / Dmax"),
 }
@@ -73,12 +75,22 @@ def parse_args():
     args = ap.parse_args()
     if not args.songs:
         args.songs = CONFIGS[args.config][1]
+    if args.config == "stress":
+        global M_WIN, TILE
+        M_WIN, TILE = 20, 8          # BASELINE configs[4]: m = 20; 64-pair tiles (a 4096 x 4096 pair is 16.6 M cells)
+        if args.pairs_per_step == 1200000:
+            args.pairs_per_step = 2000
     return args
 
 
 def make_workload(args):
     from acoss_b200 import synth
     shape, _, seed, _ = CONFIGS[args.config]
+    if args.config == "stress":   # half of the songs at 4096 frames, half drawn from 1024..4096
+        half = args.songs // 2
+        songs, labels = synth.make_song_set(shape, seed=seed, n_songs=half, fixed_length=4096)
+        s2, l2 = synth.make_song_set(shape, seed=seed + 1, n_songs=args.songs - half, length_range=(1024, 4096))
+        return songs + s2, labels + ["m" + x for x in l2]
     songs, labels = synth.make_song_set(shape, seed=seed, n_songs=args.songs)
     return songs, labels
 
@@ -97,8 +109,9 @@ def step_pairs(n_songs, per_step, step, rank, world, seed=4242):
 class TileSets:
     """Seeded tile subsets of the all-pairs tile list: step s scores tiles(s), about `per_step` pairs in total."""
 
-    def __init__(self, n_songs, lengths, per_step, T=TILE, seed=4242):
+    def __init__(self, n_songs, lengths, per_step, T=None, seed=4242):
         from acoss_b200 import parallel
+        T = TILE if T is None else T
         self.par, self.n, self.T, self.per_step, self.seed, self.lengths = parallel, n_songs, T, per_step, seed, lengths
         self.tiles = parallel.tile_list(n_songs, T)
         nt = (n_songs + T - 1) // T
@@ -126,8 +139,9 @@ class TileSets:
         return pairs, int(self.count[ids].sum()), float(load.max() / max(load.mean(), 1e-30))
 
 
-def pair_work(lengths, pairs, m=M_WIN):
+def pair_work(lengths, pairs, m=None):
     """(cells M*N, Qmax cell updates (M-2)(N-2), algorithmic bytes) summed over a pair batch."""
+    m = M_WIN if m is None else m
     M = np.maximum(lengths[pairs[:, 0]].astype(np.int64) - m + 1, 0)
     N = np.maximum(lengths[pairs[:, 1]].astype(np.int64) - m + 1, 0)
     cells = int((M * N).sum())
@@ -257,12 +271,16 @@ def run_reference(args, rank, world):
 
 def workload_config(args):
     desc = CONFIGS[args.config][3]
-    return {"workload": "%s: %d songs, 12 bins, lognormal lengths median 450 frames; a step = a seeded set of %d x %d song "
+    stress = args.config == "stress"
+    lens = "half at 4096 frames, half uniform in 1024..4096" if stress else "lognormal lengths median 450 frames"
+    return {"workload": "%s: %d songs, 12 bins, %s; a step = a seeded set of %d x %d song "
                         "tiles of the all-pairs matrix, about %d pairs in total, dealt to the GPUs by estimated cost"
-                        % (desc, args.songs, TILE, TILE, args.pairs_per_step),
+                        % (desc, args.songs, lens, TILE, TILE, args.pairs_per_step),
             "songs": args.songs, "pairs_per_step_total": args.pairs_per_step, "tile": TILE, "m": M_WIN, "kappa": KAPPA,
             "total_pairs_in_full_job": args.songs * (args.songs - 1) // 2,
-            "l2_policy": "inputs larger than L2 (0.45 GB float64 song arena at 10 000 songs, a new tile set every step)"}
+            "l2_policy": ("working set larger than L2: every pair streams two float64 matrices of windowed distances of up to "
+                          "4077 x 4077 x 8 B = 133 MB through HBM (the song arena itself is 38 MB)") if stress else
+                         "inputs larger than L2 (0.45 GB float64 song arena at 10 000 songs, a new tile set every step)"}
 
 
 # ---------------------------------------------------------------------------- B200 arm
@@ -289,7 +307,7 @@ def run_b200(args, rank, world, local):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # CPU arm first: its worker processes are forked before this process touches CUDA
         cores = os.cpu_count() or 1
-        n = args.cpu_pairs or max(64, 800 * cores)
+        n = args.cpu_pairs or (2 * cores if args.config == "stress" else max(64, 800 * cores))
         secs = cpu_reference_run(songs, step_pairs(N, n, 10_000, 0, 1), cores)
         cpu_base = {"value": n / secs, "unit": "pairs/s", "cores": cores, "kind": "port",
                     "sample": cpu_sample_desc(n, cores), "seconds": secs}
@@ -299,7 +317,7 @@ def run_b200(args, rank, world, local):
     if distributed:
         parallel.init_distributed()
     with contextlib.redirect_stdout(sys.stderr):   # the plugin prints like the reference does; stdout carries ONE JSON line
-        alg = Serra09(songs=songs, labels=labels, shortname="bench", do_memmaps=False, do_mfcc=False, device=local)
+        alg = Serra09(songs=songs, labels=labels, shortname="bench", do_memmaps=False, do_mfcc=False, device=local, m=M_WIN)
     s0, s1 = parallel.song_shares(N, world)[rank]
     alg.share_songs_allgather(range(s0, s1))   # songs resident on every GPU: shard H2D + all-gather + device-to-device
     ctx = alg._ctx["chroma"][0]
@@ -576,6 +594,8 @@ def finish_b200(v):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     traffic = None
     try:  # DRAM bytes per pair of the sweep launches, from the ncu --set full capture of the same command
+        if args.config == "stress":
+            raise KeyError("no capture for this config")
         tj = json.load(open(os.path.join(ROOT, "profiles", "r02_sweep_traffic.json")))
         traffic = tj["dram_bytes_per_pair"] * (len(batches[0][0]) if batches else 0)
     except Exception:
@@ -601,7 +621,9 @@ def finish_b200(v):
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": (achieved_tf / fp64_peak) if achieved_tf else None, "traffic": traffic,
-                     "kernel": "k_sweep7 (FP64 tensor-core dot products + integer window sums + chained row selection: "
+                     "kernel": ("k_sweep_tile + k_select_rows_cta + k_emit_crp (tiled long-song sweep, float64 SIMT, windowed "
+                                "distances through HBM)") if args.config == "stress" else
+                               "k_sweep7 (FP64 tensor-core dot products + integer window sums + chained row selection: "
                                "separators of one orientation, packed CRP of the other); k_sweep6/5/4 only for column "
                                "songs over 1015 frames",
                      "note": "FP64 roofline, NOT the bf16 figure of MEASURED_PEAKS.json (which has no FP64 entry): "
@@ -621,7 +643,7 @@ def finish_b200(v):
     }
     if v["cpu_base"] is not None:
         line["cpu_baseline"] = v["cpu_base"]
-    if world == 1:
+    if world == 1 and args.config != "stress":
         try:
             line["e2e_default_plugin"] = default_plugin_rate(args, v["songs"], v["labels"], local)
         except Exception as e:  # the headline must not depend on this extra
