@@ -68,6 +68,21 @@ struct ItemLists {
     int wide0_w = 0, wide1_w = 0;
 };
 
+// One chunk of a pair list, prepared on the host: work records, item lists, scratch totals and the pinned staging
+// image [PairWork...][items...].  Preparing chunk k + 1 overlaps the kernels of chunk k (acoss_serra09_pairs).
+struct ChunkPlan {
+    std::vector<PairWork> W;
+    ItemLists L;
+    int64_t p0 = 0;
+    int n = 0;
+    int64_t sep_total = 0, crp_total = 0, bnd_total = 0, nb_total = 0, tmat_peak = 0;
+    size_t n_items = 0, pw_bytes = 0;
+    PinBuf* stage = nullptr;
+    size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16;
+    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
+    size_t o_g70[kSweep7Buckets], o_g72[kSweep7Buckets], o_t3, o_tsel, o_t1, o_te;
+};
+
 template <int BINS, int MODE>
 int launch_sweep4(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter,
                   uint32_t flags) {
@@ -413,13 +428,17 @@ int64_t bnd_records(const acoss_ctx* c, int rows, int cols) {
     return cols > 32 * dp_cpl(c, cols) ? (int64_t)rows * 2 * 2 : 0;
 }
 
+// Host side of a chunk: work records + item lists + the staging image.  Touches no stream.
 template <int BINS>
-int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, double kappa, uint32_t flags,
-              float* qmax_raw, float* dmax_raw, float* sw_raw, int32_t* oti_out, int32_t* shape_out,
-              uint32_t* crp_out, const int64_t* crp_offsets, int32_t* crp_swapped_out) {
-    // ---- host: work records + item lists
-    std::vector<PairWork> W((size_t)n);
-    ItemLists L;
+int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, double kappa, uint32_t flags,
+               PinBuf* stage, ChunkPlan& P) {
+    P = ChunkPlan();
+    P.p0 = p0;
+    P.n = n;
+    P.stage = stage;
+    P.W.resize((size_t)n);
+    std::vector<PairWork>& W = P.W;
+    ItemLists& L = P.L;
     int64_t sep_total = 0, crp_total = 0, bnd_total = 0, nb_total = 0, tmat_total = 0, tmat_peak = 0;
     const bool tiled_ok = c->opt_tiled_wide && !c->opt_force_gscratch && tile_stride(m) >= 32 &&
                           tile_smem_bytes(m, BINS) <= (size_t)c->max_smem - 1024 && n < (1 << (kTileItemBits - 1));
@@ -571,6 +590,65 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         }
         classify_dp(c, L, (uint32_t)p, w.crp_cols);
     }
+    size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size() +
+                     L.t3.size() + L.tsel.size() + L.t1.size() + L.te.size();
+    for (int b = 0; b < kFastBuckets; ++b)
+        n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
+    for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
+    for (int b = 0; b < kG6Buckets; ++b) n_items += L.g6_0[b].size() + L.g6_2[b].size();
+    for (int b = 0; b < kSweep7Buckets; ++b) n_items += L.g7_0[b].size() + L.g7_2[b].size();
+    // stage: [PairWork...][items...]
+    const size_t pw_bytes = (size_t)n * sizeof(PairWork);
+    P.pw_bytes = pw_bytes;
+    CU(stage->reserve(pw_bytes + n_items * sizeof(uint32_t) + 64));
+    memcpy(stage->p, W.data(), pw_bytes);
+    uint32_t* hi = reinterpret_cast<uint32_t*>(stage->as<char>() + pw_bytes);
+    size_t pos = 0;
+    auto put = [&](const std::vector<uint32_t>& v) {
+        size_t at = pos;
+        if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
+        pos += v.size();
+        return at;
+    };
+    for (int b = 0; b < kFastBuckets; ++b) P.o_fast0[b] = put(L.fast0[b]);
+    for (int b = 0; b < kFastBuckets; ++b) P.o_fast2[b] = put(L.fast2[b]);
+    P.o_wide0 = put(L.wide0);
+    P.o_wide1 = put(L.wide1);
+    P.o_t3 = put(L.t3);
+    P.o_tsel = put(L.tsel);
+    P.o_t1 = put(L.t1);
+    P.o_te = put(L.te);
+    P.o_dp4 = put(L.dp4);
+    P.o_dp8 = put(L.dp8);
+    P.o_dp16 = put(L.dp16);
+    for (int b = 0; b < kFastBuckets; ++b) P.o_g40[b] = put(L.g4_0[b]);
+    for (int b = 0; b < kFastBuckets; ++b) P.o_g42[b] = put(L.g4_2[b]);
+    P.o_g4pack = put(L.g4_pack);
+    for (int b = 0; b < 2; ++b) P.o_g50[b] = put(L.g5_0[b]);
+    for (int b = 0; b < 2; ++b) P.o_g52[b] = put(L.g5_2[b]);
+    for (int b = 0; b < kG6Buckets; ++b) P.o_g60[b] = put(L.g6_0[b]);
+    for (int b = 0; b < kG6Buckets; ++b) P.o_g62[b] = put(L.g6_2[b]);
+    for (int b = 0; b < kSweep7Buckets; ++b) P.o_g70[b] = put(L.g7_0[b]);
+    for (int b = 0; b < kSweep7Buckets; ++b) P.o_g72[b] = put(L.g7_2[b]);
+    P.n_items = n_items;
+    P.sep_total = sep_total;
+    P.crp_total = crp_total;
+    P.bnd_total = bnd_total;
+    P.nb_total = nb_total;
+    P.tmat_peak = tmat_peak;
+    return ACOSS_OK;
+}
+
+// Device side of a prepared chunk: scratch, staging copies, kernels, result copies.  Asynchronous on c->stream.
+template <int BINS>
+int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, float* qmax_raw, float* dmax_raw, float* sw_raw,
+               bool want_oti, bool want_crp) {
+    const ItemLists& L = P.L;
+    const int n = P.n;
+    const int64_t p0 = P.p0, sep_total = P.sep_total, crp_total = P.crp_total, bnd_total = P.bnd_total,
+                  nb_total = P.nb_total, tmat_peak = P.tmat_peak;
+    const size_t n_items = P.n_items, pw_bytes = P.pw_bytes;
+    const uint32_t* hi = reinterpret_cast<const uint32_t*>(P.stage->as<char>() + pw_bytes);
     // ---- device buffers
     CU(c->pairs.reserve((size_t)n * sizeof(PairWork)));
     CU(c->seps.reserve((size_t)std::max<int64_t>(sep_total, 1) * sizeof(double)));
@@ -587,46 +665,8 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         CU(c->nb.reserve((size_t)std::max<int64_t>(nb_total, 16)));
     }
     if (tmat_peak > 0) CU(c->tmat.reserve((size_t)tmat_peak * sizeof(double)));
-    size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size() +
-                     L.t3.size() + L.tsel.size() + L.t1.size() + L.te.size();
-    for (int b = 0; b < kFastBuckets; ++b)
-        n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
-    for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
-    for (int b = 0; b < kG6Buckets; ++b) n_items += L.g6_0[b].size() + L.g6_2[b].size();
-    for (int b = 0; b < kSweep7Buckets; ++b) n_items += L.g7_0[b].size() + L.g7_2[b].size();
     CU(c->items.reserve(std::max<size_t>(n_items, 1) * sizeof(uint32_t)));
-    // stage: [PairWork...][items...]
-    const size_t pw_bytes = (size_t)n * sizeof(PairWork);
-    CU(c->h_stage.reserve(pw_bytes + n_items * sizeof(uint32_t) + 64));
-    memcpy(c->h_stage.p, W.data(), pw_bytes);
-    uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_stage.as<char>() + pw_bytes);
-    size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16, pos = 0;
-    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
-    size_t o_g70[kSweep7Buckets], o_g72[kSweep7Buckets];
-    auto put = [&](const std::vector<uint32_t>& v) {
-        size_t at = pos;
-        if (!v.empty()) memcpy(hi + pos, v.data(), v.size() * sizeof(uint32_t));
-        pos += v.size();
-        return at;
-    };
-    for (int b = 0; b < kFastBuckets; ++b) o_fast0[b] = put(L.fast0[b]);
-    for (int b = 0; b < kFastBuckets; ++b) o_fast2[b] = put(L.fast2[b]);
-    o_wide0 = put(L.wide0);
-    o_wide1 = put(L.wide1);
-    const size_t o_t3 = put(L.t3), o_tsel = put(L.tsel), o_t1 = put(L.t1), o_te = put(L.te);
-    o_dp4 = put(L.dp4);
-    o_dp8 = put(L.dp8);
-    o_dp16 = put(L.dp16);
-    for (int b = 0; b < kFastBuckets; ++b) o_g40[b] = put(L.g4_0[b]);
-    for (int b = 0; b < kFastBuckets; ++b) o_g42[b] = put(L.g4_2[b]);
-    o_g4pack = put(L.g4_pack);
-    for (int b = 0; b < 2; ++b) o_g50[b] = put(L.g5_0[b]);
-    for (int b = 0; b < 2; ++b) o_g52[b] = put(L.g5_2[b]);
-    for (int b = 0; b < kG6Buckets; ++b) o_g60[b] = put(L.g6_0[b]);
-    for (int b = 0; b < kG6Buckets; ++b) o_g62[b] = put(L.g6_2[b]);
-    for (int b = 0; b < kSweep7Buckets; ++b) o_g70[b] = put(L.g7_0[b]);
-    for (int b = 0; b < kSweep7Buckets; ++b) o_g72[b] = put(L.g7_2[b]);
-    CU(cudaMemcpyAsync(c->pairs.p, c->h_stage.p, pw_bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->pairs.p, P.stage->p, pw_bytes, cudaMemcpyHostToDevice, c->stream));
     if (n_items)
         CU(cudaMemcpyAsync(c->items.p, hi, n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemsetAsync(c->counters.p, 0, kCounterSlots * sizeof(unsigned int), c->stream));
@@ -681,51 +721,51 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
             c->stream = c->stream2;
         }
         // largest buckets first: their CTAs are the long ones
-        if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
+        if ((rc = launch_sweep<BINS, 256, 0>(c, d_items + P.o_wide0, (int)L.wide0.size(), L.wide0_w, m, d_cnt + kFastBuckets, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)
-            if ((rc = launch_sweep_fast<BINS, 0>(c, d_items + o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
+            if ((rc = launch_sweep_fast<BINS, 0>(c, d_items + P.o_fast0[b], (int)L.fast0[b].size(), b, m, d_cnt + b, flags))) return rc;
         for (size_t wv = 0; wv < L.wave_t3.size(); ++wv) {
             const size_t a3 = L.wave_t3[wv], b3 = wv + 1 < L.wave_t3.size() ? L.wave_t3[wv + 1] : L.t3.size();
             const size_t as = L.wave_tsel[wv], bs = wv + 1 < L.wave_tsel.size() ? L.wave_tsel[wv + 1] : L.tsel.size();
             const size_t ae = L.wave_te[wv], be = wv + 1 < L.wave_te.size() ? L.wave_te[wv + 1] : L.te.size();
             if (wv > 0) CU(cudaMemsetAsync(d_cnt + 72, 0, sizeof(unsigned int), c->stream));  // the wave's work-queue head
-            if ((rc = launch_sweep_tile<BINS, 3>(c, d_items + o_t3 + a3, (int)(b3 - a3), m, d_cnt + 72, flags))) return rc;
-            if ((rc = launch_select_rows(c, d_items + o_tsel + as, (int)(bs - as), L.tsel_rows, L.tsel_cols, m))) return rc;
-            if ((rc = launch_emit_crp(c, d_items + o_te + ae, (int)(be - ae), L.te_rows, m, flags))) return rc;
+            if ((rc = launch_sweep_tile<BINS, 3>(c, d_items + P.o_t3 + a3, (int)(b3 - a3), m, d_cnt + 72, flags))) return rc;
+            if ((rc = launch_select_rows(c, d_items + P.o_tsel + as, (int)(bs - as), L.tsel_rows, L.tsel_cols, m))) return rc;
+            if ((rc = launch_emit_crp(c, d_items + P.o_te + ae, (int)(be - ae), L.te_rows, m, flags))) return rc;
         }
-        if ((rc = launch_sweep_tile<BINS, 1>(c, d_items + o_t1, (int)L.t1.size(), m, d_cnt + 73, flags))) return rc;
-        if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
+        if ((rc = launch_sweep_tile<BINS, 1>(c, d_items + P.o_t1, (int)L.t1.size(), m, d_cnt + 73, flags))) return rc;
+        if ((rc = launch_sweep<BINS, 256, 1>(c, d_items + P.o_wide1, (int)L.wide1.size(), L.wide1_w, m, d_cnt + 2 * kFastBuckets + 1, flags))) return rc;
         for (int b = kFastBuckets - 1; b >= 0; --b)
-            if ((rc = launch_sweep_fast<BINS, 2>(c, d_items + o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
+            if ((rc = launch_sweep_fast<BINS, 2>(c, d_items + P.o_fast2[b], (int)L.fast2[b].size(), b, m, d_cnt + kFastBuckets + 1 + b, flags))) return rc;
         if (side) CU(cudaEventRecord(c->ev_side, c->stream2));
     }
     for (int b = kSweep7Buckets - 1; b >= 0; --b)
-        if ((rc = acoss_launch_sweep7(c, 0, BINS, d_items + o_g70[b], (int)L.g7_0[b].size(), b, d_cnt + 80 + b, flags))) return rc;
+        if ((rc = acoss_launch_sweep7(c, 0, BINS, d_items + P.o_g70[b], (int)L.g7_0[b].size(), b, d_cnt + 80 + b, flags))) return rc;
     for (int b = kG6Buckets - 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep6<0>(c, d_items + o_g60[b], (int)L.g6_0[b].size(), b, m, d_cnt + 64 + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep6<0>(c, d_items + P.o_g60[b], (int)L.g6_0[b].size(), b, m, d_cnt + 64 + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep5<0>(c, d_items + o_g50[b], (int)L.g5_0[b].size(), b + 1, m, d_cnt + 56 + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep5<0>(c, d_items + P.o_g50[b], (int)L.g5_0[b].size(), b + 1, m, d_cnt + 56 + b, flags))) return rc;
     for (int b = kFastBuckets - 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + P.o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
     for (int b = kSweep7Buckets - 1; b >= 0; --b)
-        if ((rc = acoss_launch_sweep7(c, 2, BINS, d_items + o_g72[b], (int)L.g7_2[b].size(), b, d_cnt + 80 + kSweep7Buckets + b, flags))) return rc;
+        if ((rc = acoss_launch_sweep7(c, 2, BINS, d_items + P.o_g72[b], (int)L.g7_2[b].size(), b, d_cnt + 80 + kSweep7Buckets + b, flags))) return rc;
     for (int b = kG6Buckets - 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep6<2>(c, d_items + o_g62[b], (int)L.g6_2[b].size(), b, m, d_cnt + 64 + kG6Buckets + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep6<2>(c, d_items + P.o_g62[b], (int)L.g6_2[b].size(), b, m, d_cnt + 64 + kG6Buckets + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep5<2>(c, d_items + o_g52[b], (int)L.g5_2[b].size(), b + 1, m, d_cnt + 58 + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep5<2>(c, d_items + P.o_g52[b], (int)L.g5_2[b].size(), b + 1, m, d_cnt + 58 + b, flags))) return rc;
     for (int b = kFastBuckets - 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep4<12, 2>(c, d_items + o_g42[b], (int)L.g4_2[b].size(), b, m, d_cnt + 32 + kFastBuckets + b, flags))) return rc;
+        if (BINS == 12 && (rc = launch_sweep4<12, 2>(c, d_items + P.o_g42[b], (int)L.g4_2[b].size(), b, m, d_cnt + 32 + kFastBuckets + b, flags))) return rc;
     if (!L.g4_pack.empty()) {
         auto kp = k_nb_to_packed;
-        ACOSS_LAUNCH(kp, (int)L.g4_pack.size(), 128, 0, c->stream, c->pairs.as<PairWork>(), d_items + o_g4pack,
+        ACOSS_LAUNCH(kp, (int)L.g4_pack.size(), 128, 0, c->stream, c->pairs.as<PairWork>(), d_items + P.o_g4pack,
                      (int)L.g4_pack.size(), c->nb.as<uint8_t>(), c->crp.as<uint32_t>(), m);
         c->launches++;
         CU(cudaGetLastError());
     }
     if (side) CU(cudaStreamWaitEvent(c->stream, c->ev_side, 0));
     CU(cudaEventRecord(c->ev[3], c->stream));
-    if ((rc = run_dp_lists(c, L, d_items, o_dp4, o_dp8, o_dp16, flags))) return rc;
+    if ((rc = run_dp_lists(c, L, d_items, P.o_dp4, P.o_dp8, P.o_dp16, flags))) return rc;
     CU(cudaEventRecord(c->ev[4], c->stream));
 
     // ---- results
@@ -733,14 +773,23 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
     if (dmax_raw) CU(cudaMemcpyAsync(dmax_raw + p0, c->dout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     if (sw_raw && (flags & kFlagWantSw))
         CU(cudaMemcpyAsync(sw_raw + p0, c->swout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
-    if (oti_out || crp_swapped_out) {
+    if (want_oti) {
         // the oti lives in the PairWork records
-        CU(cudaMemcpyAsync(c->h_stage.p, c->pairs.p, pw_bytes, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(P.stage->p, c->pairs.p, pw_bytes, cudaMemcpyDeviceToHost, c->stream));
     }
-    if (crp_out) {
+    if (want_crp) {
         c->h_crp.resize((size_t)std::max<int64_t>(crp_total, 1));
         CU(cudaMemcpyAsync(c->h_crp.data(), c->crp.p, (size_t)crp_total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     }
+    return ACOSS_OK;
+}
+
+// Wait for a chunk, add its stage times, hand the host-side results out.
+int finish_chunk(acoss_ctx* c, const ChunkPlan& P, uint32_t flags, float* sw_raw, int32_t* oti_out, int32_t* shape_out,
+                 uint32_t* crp_out, const int64_t* crp_offsets, int32_t* crp_swapped_out) {
+    const std::vector<PairWork>& W = P.W;
+    const int64_t p0 = P.p0;
+    const int n = P.n;
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     for (int s = 0; s < 4; ++s) {
@@ -753,7 +802,7 @@ int run_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, doub
         CU(cudaEventElapsedTime(&ms, c->ev[0], c->ev[4]));
         c->stage_ms[4] += ms;
     }
-    const PairWork* back = c->h_stage.as<PairWork>();
+    const PairWork* back = P.stage->as<PairWork>();
     for (int p = 0; p < n; ++p) {
         if (oti_out) oti_out[p0 + p] = back[p].oti;
         if (crp_swapped_out) crp_swapped_out[p0 + p] = W[p].swap;
@@ -828,6 +877,7 @@ int acoss_destroy(acoss_ctx* c) {
                       &c->frames2, &c->snf_desc, &c->snf_mats, &c->snf_md, &c->snf_sidx, &c->snf_sval};
     for (DevBuf* b : bufs) b->release();
     c->h_stage.release();
+    c->h_stage2.release();
     for (int i = 0; i < 5; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->ev_prep) cudaEventDestroy(c->ev_prep);
@@ -916,9 +966,9 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
     for (int s = 0; s < 5; ++s) c->stage_ms[s] = 0.f;
     c->have_stage_ms = true;
     flags |= c->opt_debug_flags;
-    int64_t p0 = 0;
-    while (p0 < P) {
-        // cut a chunk whose scratch fits the budget
+    // Chunks whose scratch fits the budget.  The host side of chunk k + 1 (work records, item lists, staging image)
+    // is prepared while the kernels of chunk k run; two pinned staging buffers alternate.
+    auto cut = [&](int64_t p0) {
         int n = 0;
         int64_t sep = 0, crp = 0, nbb = 0;
         while (p0 + n < P && n < c->opt_chunk_pairs) {
@@ -932,14 +982,34 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
             nbb += n2;
             ++n;
         }
-        if (c->bins == 12)
-            rc = run_chunk<12>(c, pairs, p0, n, m, kappa, flags, qmax_raw, dmax_raw, sw_raw, oti_out, shape_out,
-                               crp_out, crp_offsets, crp_swapped_out);
-        else
-            rc = run_chunk<13>(c, pairs, p0, n, m, kappa, flags, qmax_raw, dmax_raw, sw_raw, oti_out, shape_out,
-                               crp_out, crp_offsets, crp_swapped_out);
-        if (rc) return rc;
-        p0 += n;
+        return n;
+    };
+    auto prep = [&](int64_t p0, int n, PinBuf* stage, ChunkPlan& plan) {
+        return c->bins == 12 ? prep_chunk<12>(c, pairs, p0, n, m, kappa, flags, stage, plan)
+                             : prep_chunk<13>(c, pairs, p0, n, m, kappa, flags, stage, plan);
+    };
+    const bool want_oti = oti_out || crp_swapped_out;
+    ChunkPlan plans[2];
+    PinBuf* stages[2] = {&c->h_stage, &c->h_stage2};
+    int cur = 0;
+    int64_t p0 = 0;
+    if (P > 0 && (rc = prep(0, cut(0), stages[0], plans[0]))) return rc;
+    while (p0 < P) {
+        ChunkPlan& plan = plans[cur];
+        rc = c->bins == 12 ? exec_chunk<12>(c, plan, m, flags, qmax_raw, dmax_raw, sw_raw, want_oti, crp_out != nullptr)
+                           : exec_chunk<13>(c, plan, m, flags, qmax_raw, dmax_raw, sw_raw, want_oti, crp_out != nullptr);
+        const int64_t next = p0 + plan.n;
+        int rc2 = ACOSS_OK;
+        if (!rc && next < P) rc2 = prep(next, cut(next), stages[cur ^ 1], plans[cur ^ 1]);
+        if (rc || rc2) {
+            const std::string msg = acoss_error_slot();
+            cudaStreamSynchronize(c->stream);  // nothing of this call stays in flight
+            acoss_error_slot() = msg;
+            return rc ? rc : rc2;
+        }
+        if ((rc = finish_chunk(c, plan, flags, sw_raw, oti_out, shape_out, crp_out, crp_offsets, crp_swapped_out))) return rc;
+        p0 = next;
+        cur ^= 1;
     }
     return ACOSS_OK;
 }

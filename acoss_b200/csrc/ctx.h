@@ -111,7 +111,7 @@ struct acoss_ctx {
     DevBuf tmat;                                // tiled long-song sweep: float64 T matrices of the chunk
     DevBuf lens, wnorm, wnmax, sepk, sepx, nb;  // gen-4 sweep: windowed norms, integer separators, nibble CRPs
     int wnorm_m = -1;                           // window the wnorm buffer was computed for
-    PinBuf h_stage;
+    PinBuf h_stage, h_stage2;  // pinned staging images of two consecutive chunks
     std::vector<uint32_t> h_crp;
     // test/tuning knobs (acoss_set_option)
     int opt_force_wide = 0;      // send every sweep item through the 256-thread kernels

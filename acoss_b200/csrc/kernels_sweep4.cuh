@@ -782,7 +782,9 @@ __device__ __forceinline__ void s4_resolve_row(const Sweep4Args& A, const S4Pair
                 rblo = vk - 3;
                 thr = rblo - 1;
             } else {
-                thr = vk;  // tie cluster: the reference's own choice is undefined here
+                // tie cluster (the reference's own choice is undefined here): equal keys across the k-th position are
+                // all left out, like the float64 kernels do (warp_select_sep); fewer than k neighbours
+                thr = (vk1 == vk) ? vk - 1 : vk;
                 ncand = 0;
             }
         }

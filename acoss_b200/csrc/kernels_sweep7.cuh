@@ -526,7 +526,9 @@ __global__ void __launch_bounds__(NT, (S7Cfg<NT, CPT>::MINB)) k_sweep7(Sweep7Arg
                                     rsepx[srow] = sx;
                                 }
                             } else {
-                                thr = vk;  // tie cluster: the reference's own choice is undefined here
+                                // tie cluster (the reference's own choice is undefined here): equal keys across the k-th position are
+                                // all left out, like the float64 kernels do (warp_select_sep); fewer than k neighbours
+                                thr = (vk1 == vk) ? vk - 1 : vk;
                             }
                             prev_abs = vk + kwx;
 #if ACOSS_S7_STAT

@@ -210,3 +210,49 @@ def check_symmetry(ctx, songs, n_pairs=200, seed=3, m=9, kappa=0.095):
     assert np.array_equal(a["qmax_raw"][same], b["qmax_raw"][same])
     assert np.array_equal(a["dmax_raw"][same], b["dmax_raw"][same])
     return int(same.sum())
+
+
+def check_ties_golden(ctx, G):
+    """Songs with exactly repeated frames (tests/golden/ties_golden.npz, reference-produced by
+    oracle/make_golden_ties.py).  Where equal distances straddle the k-th neighbour the reference keeps exactly k
+    (argpartition's pick among the tied cells follows the rounding noise of its cumsum differences), the product keeps
+    the cells strictly below the separator: DESIGN.md section 2, deviation 1.  Asserted: OTI; every cell whose row and
+    column are both untied; whole plots and scores of the pairs without a tied line.  Counted and returned: the cells
+    and scores that differ on tied lines."""
+    m, kappa = int(G["m"]), float(G["kappa"])
+    st = {"pairs": 0, "pairs_tied": 0, "cells": 0, "cells_on_tied_lines": 0, "bits_missing": 0, "bits_extra": 0,
+          "ones_ref": 0, "qmax_rel": [], "dmax_rel": [], "pairs_score_equal": 0}
+    for tag, n, npairs in G["cases"].tolist():
+        songs = [{"chroma": G["%s_chroma_%d" % (tag, s)], "gchroma": G["%s_gchroma_%d" % (tag, s)]} for s in range(n)]
+        ctx.upload_songs(songs)
+        pairs = np.array([G["%s_p%d_ij" % (tag, p)] for p in range(npairs)])
+        r = ctx.serra09_pairs(pairs, m=m, kappa=kappa, flags=_native.FLAG_NO_SWAP, want_crp=True)
+        for p in range(npairs):
+            key = "%s_p%d" % (tag, p)
+            M, N = G[key + "_shape"]
+            ref = crp_oracle.unpack_bits(G[key + "_crp"], N)
+            rows = np.unpackbits(G[key + "_tied_rows"])[:M].astype(bool)
+            cols = np.unpackbits(G[key + "_tied_cols"])[:N].astype(bool)
+            sc = G[key + "_scores"]
+            got = r["crp"][p]
+            where = "ties case %s pair %d" % (tag, p)
+            assert tuple(r["shape"][p]) == (M, N), where
+            assert r["oti"][p] == int(G[key + "_oti"]), where
+            clean = ~rows[:, None] & ~cols[None, :]
+            assert np.array_equal(got[clean], ref[clean]), where + ": %d bits differ off the tied lines" % int(
+                (got[clean] != ref[clean]).sum())
+            st["pairs"] += 1
+            st["cells"] += int(M) * int(N)
+            st["ones_ref"] += int(ref.sum())
+            if rows.any() or cols.any():
+                st["pairs_tied"] += 1
+                st["cells_on_tied_lines"] += int((~clean).sum())
+                st["bits_missing"] += int((ref & ~got & 1).sum())
+                st["bits_extra"] += int((got & ~ref & 1).sum())
+                st["qmax_rel"].append(abs(float(r["qmax_raw"][p]) - sc[0]) / max(sc[0], 1.0))
+                st["dmax_rel"].append(abs(float(r["dmax_raw"][p]) - sc[1]) / max(sc[1], 1.0))
+                st["pairs_score_equal"] += int(r["qmax_raw"][p] == sc[0] and r["dmax_raw"][p] == sc[1])
+            else:
+                assert np.array_equal(got, ref), where
+                assert r["qmax_raw"][p] == sc[0] and r["dmax_raw"][p] == sc[1], where
+    return st
