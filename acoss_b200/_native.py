@@ -59,6 +59,7 @@ SIGNATURES = {
     "acoss_kernel_launches": (ctypes.c_int64, [ctypes.c_void_p]),
     "acoss_reset_counters": (None, [ctypes.c_void_p]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
+    "acoss_debug_host_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
     "acoss_upload_aux_songs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int32]),
     "acoss_snf_pairs": (ctypes.c_int, [ctypes.c_void_p, _c_i32p, ctypes.c_int64, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
@@ -435,6 +436,11 @@ class Context:
 
     def reset_counters(self):
         self.lib.acoss_reset_counters(self._h)
+
+    def debug_host_ms(self):
+        out = np.zeros(6, np.float32)
+        self._check(self.lib.acoss_debug_host_ms(self._h, _ptr(out, _c_f32p)), "acoss_debug_host_ms")
+        return dict(zip(["call", "first_prep", "issue", "overlapped_prep", "wait", "results"], out.tolist()))
 
     def last_stage_ms(self):
         out = np.zeros(5, np.float32)

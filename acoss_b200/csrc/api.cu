@@ -4,6 +4,7 @@
 //   k_oti -> k_sweep<MODE 0> (both orientations) -> k_sweep<MODE 1> -> k_dp.
 // There is no CPU path: every entry point fails with ACOSS_ERR_CUDA when the device is
 // missing or a launch fails.
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -76,7 +77,7 @@ struct ChunkPlan {
     int64_t p0 = 0;
     int n = 0;
     int64_t sep_total = 0, crp_total = 0, bnd_total = 0, nb_total = 0, tmat_peak = 0;
-    size_t n_items = 0, pw_bytes = 0;
+    size_t n_items = 0, pw_bytes = 0, res_off = 0;   // res_off: float results [q | d | sw] of n each in the staging image
     PinBuf* stage = nullptr;
     size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16;
     size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
@@ -600,7 +601,10 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
     // stage: [PairWork...][items...]
     const size_t pw_bytes = (size_t)n * sizeof(PairWork);
     P.pw_bytes = pw_bytes;
-    CU(stage->reserve(pw_bytes + n_items * sizeof(uint32_t) + 64));
+    // (results come back into the same pinned image: a device-to-host copy into the caller's pageable arrays would
+    // block the issuing thread until the chunk's kernels are done, and with it the preparation of the next chunk)
+    P.res_off = (pw_bytes + n_items * sizeof(uint32_t) + 63) & ~(size_t)63;
+    CU(stage->reserve(P.res_off + 3 * (size_t)n * sizeof(float) + 64));
     memcpy(stage->p, W.data(), pw_bytes);
     uint32_t* hi = reinterpret_cast<uint32_t*>(stage->as<char>() + pw_bytes);
     size_t pos = 0;
@@ -641,11 +645,11 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
 
 // Device side of a prepared chunk: scratch, staging copies, kernels, result copies.  Asynchronous on c->stream.
 template <int BINS>
-int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, float* qmax_raw, float* dmax_raw, float* sw_raw,
-               bool want_oti, bool want_crp) {
+int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, const float* qmax_raw, const float* dmax_raw,
+               const float* sw_raw, bool want_oti, bool want_crp) {
     const ItemLists& L = P.L;
     const int n = P.n;
-    const int64_t p0 = P.p0, sep_total = P.sep_total, crp_total = P.crp_total, bnd_total = P.bnd_total,
+    const int64_t sep_total = P.sep_total, crp_total = P.crp_total, bnd_total = P.bnd_total,
                   nb_total = P.nb_total, tmat_peak = P.tmat_peak;
     const size_t n_items = P.n_items, pw_bytes = P.pw_bytes;
     const uint32_t* hi = reinterpret_cast<const uint32_t*>(P.stage->as<char>() + pw_bytes);
@@ -769,10 +773,11 @@ int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, float* qmax_ra
     CU(cudaEventRecord(c->ev[4], c->stream));
 
     // ---- results
-    if (qmax_raw) CU(cudaMemcpyAsync(qmax_raw + p0, c->qout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
-    if (dmax_raw) CU(cudaMemcpyAsync(dmax_raw + p0, c->dout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    float* res = reinterpret_cast<float*>(P.stage->as<char>() + P.res_off);
+    if (qmax_raw) CU(cudaMemcpyAsync(res, c->qout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    if (dmax_raw) CU(cudaMemcpyAsync(res + n, c->dout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     if (sw_raw && (flags & kFlagWantSw))
-        CU(cudaMemcpyAsync(sw_raw + p0, c->swout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(res + 2 * (size_t)n, c->swout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     if (want_oti) {
         // the oti lives in the PairWork records
         CU(cudaMemcpyAsync(P.stage->p, c->pairs.p, pw_bytes, cudaMemcpyDeviceToHost, c->stream));
@@ -784,14 +789,12 @@ int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, float* qmax_ra
     return ACOSS_OK;
 }
 
-// Wait for a chunk, add its stage times, hand the host-side results out.
-int finish_chunk(acoss_ctx* c, const ChunkPlan& P, uint32_t flags, float* sw_raw, int32_t* oti_out, int32_t* shape_out,
-                 uint32_t* crp_out, const int64_t* crp_offsets, int32_t* crp_swapped_out) {
-    const std::vector<PairWork>& W = P.W;
-    const int64_t p0 = P.p0;
-    const int n = P.n;
+// Wait for a chunk and add its stage times.
+int wait_chunk(acoss_ctx* c) {
+    auto t0 = std::chrono::steady_clock::now();
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
+    c->host_ms[4] += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     for (int s = 0; s < 4; ++s) {
         float ms = 0.f;
         CU(cudaEventElapsedTime(&ms, c->ev[s], c->ev[s + 1]));
@@ -802,6 +805,26 @@ int finish_chunk(acoss_ctx* c, const ChunkPlan& P, uint32_t flags, float* sw_raw
         CU(cudaEventElapsedTime(&ms, c->ev[0], c->ev[4]));
         c->stage_ms[4] += ms;
     }
+    return ACOSS_OK;
+}
+
+// Hand a finished chunk's results (pinned staging image, host records) to the caller's arrays.
+int deliver_chunk(acoss_ctx* c, const ChunkPlan& P, uint32_t flags, float* qmax_raw, float* dmax_raw, float* sw_raw,
+                  int32_t* oti_out, int32_t* shape_out, uint32_t* crp_out, const int64_t* crp_offsets,
+                  int32_t* crp_swapped_out) {
+    const std::vector<PairWork>& W = P.W;
+    const int64_t p0 = P.p0;
+    const int n = P.n;
+    const auto t0 = std::chrono::steady_clock::now();
+    struct Lap {
+        acoss_ctx* c;
+        std::chrono::steady_clock::time_point t0;
+        ~Lap() { c->host_ms[5] += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+    } lap{c, t0};
+    const float* res = reinterpret_cast<const float*>(P.stage->as<char>() + P.res_off);
+    if (qmax_raw) memcpy(qmax_raw + p0, res, (size_t)n * sizeof(float));
+    if (dmax_raw) memcpy(dmax_raw + p0, res + n, (size_t)n * sizeof(float));
+    if (sw_raw && (flags & kFlagWantSw)) memcpy(sw_raw + p0, res + 2 * (size_t)n, (size_t)n * sizeof(float));
     const PairWork* back = P.stage->as<PairWork>();
     for (int p = 0; p < n; ++p) {
         if (oti_out) oti_out[p0 + p] = back[p].oti;
@@ -950,6 +973,7 @@ int acoss_upload_songs(acoss_ctx* c, const void* frames, int dtype, const int64_
 int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m, double kappa, uint32_t flags,
                         float* qmax_raw, float* dmax_raw, float* sw_raw, int32_t* oti_out, int32_t* shape_out,
                         uint32_t* crp_out, const int64_t* crp_offsets, int32_t* crp_swapped_out) {
+    const auto t_call = std::chrono::steady_clock::now();
     int rc = check_ctx(c);
     if (rc) return rc;
     if (c->n_songs <= 0) return fail(ACOSS_ERR_STATE, "acoss_upload_songs has not been called");
@@ -989,28 +1013,55 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
                              : prep_chunk<13>(c, pairs, p0, n, m, kappa, flags, stage, plan);
     };
     const bool want_oti = oti_out || crp_swapped_out;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [&](std::chrono::steady_clock::time_point t) {
+        return std::chrono::duration<float, std::milli>(now() - t).count();
+    };
+    for (float& v : c->host_ms) v = 0.f;
     ChunkPlan plans[2];
     PinBuf* stages[2] = {&c->h_stage, &c->h_stage2};
     int cur = 0;
     int64_t p0 = 0;
+    auto t_prep = now();
     if (P > 0 && (rc = prep(0, cut(0), stages[0], plans[0]))) return rc;
+    c->host_ms[1] = ms_since(t_prep);
+    int pending = -1;   // chunk waited for but not yet delivered: its results go out under the next chunk's kernels
+    auto deliver = [&](int k) {
+        return deliver_chunk(c, plans[k], flags, qmax_raw, dmax_raw, sw_raw, oti_out, shape_out, crp_out, crp_offsets,
+                             crp_swapped_out);
+    };
     while (p0 < P) {
         ChunkPlan& plan = plans[cur];
+        auto t_exec = now();
         rc = c->bins == 12 ? exec_chunk<12>(c, plan, m, flags, qmax_raw, dmax_raw, sw_raw, want_oti, crp_out != nullptr)
                            : exec_chunk<13>(c, plan, m, flags, qmax_raw, dmax_raw, sw_raw, want_oti, crp_out != nullptr);
+        c->host_ms[2] += ms_since(t_exec);
         const int64_t next = p0 + plan.n;
         int rc2 = ACOSS_OK;
-        if (!rc && next < P) rc2 = prep(next, cut(next), stages[cur ^ 1], plans[cur ^ 1]);
+        t_prep = now();
+        if (!rc && pending >= 0) {
+            rc2 = deliver(pending);
+            pending = -1;
+        }
+        if (!rc && !rc2 && next < P) rc2 = prep(next, cut(next), stages[cur ^ 1], plans[cur ^ 1]);
+        c->host_ms[3] += ms_since(t_prep);
         if (rc || rc2) {
             const std::string msg = acoss_error_slot();
             cudaStreamSynchronize(c->stream);  // nothing of this call stays in flight
             acoss_error_slot() = msg;
             return rc ? rc : rc2;
         }
-        if ((rc = finish_chunk(c, plan, flags, sw_raw, oti_out, shape_out, crp_out, crp_offsets, crp_swapped_out))) return rc;
+        if ((rc = wait_chunk(c))) return rc;
+        if (crp_out) {   // the plots come back through one host buffer: hand them out before the next chunk reuses it
+            if ((rc = deliver(cur))) return rc;
+        } else {
+            pending = cur;
+        }
         p0 = next;
         cur ^= 1;
     }
+    if (pending >= 0 && (rc = deliver(pending))) return rc;
+    c->host_ms[0] = ms_since(t_call);
     return ACOSS_OK;
 }
 
@@ -1520,6 +1571,12 @@ int acoss_debug_sweep7_stats(acoss_ctx* c, uint64_t out[16], int reset) {
     const int rc = acoss_sweep7_stats(c, h, reset);
     for (int i = 0; i < 16; ++i) out[i] = h[i];
     return rc;
+}
+
+int acoss_debug_host_ms(acoss_ctx* c, float out[6]) {
+    if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
+    for (int s = 0; s < 6; ++s) out[s] = c->host_ms[s];
+    return ACOSS_OK;
 }
 
 int acoss_last_stage_ms(acoss_ctx* c, float out[5]) {

@@ -137,6 +137,7 @@ struct acoss_ctx {
     // accounting
     int64_t launches = 0;
     float stage_ms[5] = {0, 0, 0, 0, 0};
+    float host_ms[6] = {0, 0, 0, 0, 0, 0};  // host wall times of the last acoss_serra09_pairs call (acoss_debug_host_ms)
     bool have_stage_ms = false;
     float eval_ms = -1.f;  // device time of the last k_eval_ranks launch
     DevBuf eval_D;         // score matrix of acoss_eval_ranks when it arrives from the host

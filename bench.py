@@ -352,10 +352,13 @@ def run_b200(args, rank, world, local):
     if rank == 0:
         sampler.start()
     t0 = time.perf_counter()
+    host = {}
     for pairs, _, _ in batches:
         ctx.serra09_pairs(pairs, m=M_WIN, kappa=KAPPA)   # synchronises its stream before returning
         for k, v in ctx.last_stage_ms().items():
             stage[k] += v
+        for k, v in ctx.debug_host_ms().items():
+            host[k] = host.get(k, 0.0) + v
     busy = time.perf_counter() - t0                      # this rank's own time, before waiting for the others
     barrier()
     dt = time.perf_counter() - t0
@@ -624,6 +627,7 @@ def finish_b200(v):
         "qmax_dmax_gcups_dp_kernel": dp_gcups,
         "cells_per_sec": cells / dt,
         "device_ms_per_step": {k: x / steps for k, x in stage.items()},
+        "host_ms_per_step": {k: x / steps for k, x in v["host"].items()},
         "clocks": clocks,
         "lpt_imbalance": v["imbalance"],
         "rank_busy_ms_per_step": {"max": 1e3 * busy_max / steps, "min": 1e3 * float(tmin[0]) / steps},

@@ -244,6 +244,11 @@ int acoss_debug_sweep6_cycles(acoss_ctx* ctx, uint64_t out[8], int reset);
  * built with -DACOSS_S7_STATS. */
 int acoss_debug_sweep7_stats(acoss_ctx* ctx, uint64_t out[16], int reset);
 
+/* Profiling aid: host wall times (ms) of the last acoss_serra09_pairs call: [0] whole call, [1] preparing the first
+ * chunk (not overlapped), [2] issuing copies + launches, [3] preparing chunks 2.. and handing out earlier results (overlapped with kernels),
+ * [4] waiting for the stream, [5] handing results out (mostly inside [3]). */
+int acoss_debug_host_ms(acoss_ctx* ctx, float out[6]);
+
 /* Counters for bench.py: kernels launched by this context since creation / last reset. */
 int64_t acoss_kernel_launches(acoss_ctx* ctx);
 void acoss_reset_counters(acoss_ctx* ctx);
