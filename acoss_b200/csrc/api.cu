@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "kernels_dense.cuh"
 #include "kernels_dp.cuh"
+#include "kernels_dp16.cuh"
 #include "kernels_prep.cuh"
 #include "kernels_sweep.cuh"
 #include "kernels_sweep1t.cuh"
@@ -66,6 +67,7 @@ struct ItemLists {
     std::vector<uint32_t> g7_0[kSweep7Buckets], g7_2[kSweep7Buckets];  // gen-7 sweep by column capacity
     bool have_keys = false;                                          // some pair uses the integer-key sweeps
     std::vector<uint32_t> dp4, dp8, dp16;
+    bool dp_packed_ok = true;                                        // every plot fits the 16-bit lanes of k_dp16
     int wide0_w = 0, wide1_w = 0;
 };
 
@@ -376,7 +378,8 @@ int launch_sweep6(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket
 }
 
 template <int CPL>
-int launch_dp(acoss_ctx* c, const uint32_t* d_items, int n_items, uint32_t flags, float* q, float* d, float* sw) {
+int launch_dp(acoss_ctx* c, const uint32_t* d_items, int n_items, uint32_t flags, float* q, float* d, float* sw,
+              bool packed_ok) {
     if (n_items <= 0) return ACOSS_OK;
     DpArgs A;
     A.pairs = c->pairs.as<PairWork>();
@@ -391,6 +394,9 @@ int launch_dp(acoss_ctx* c, const uint32_t* d_items, int n_items, uint32_t flags
     const int grid = (n_items + 3) / 4;
     if (flags & kFlagWantSw) {
         auto kfn = k_dp<CPL, true>;
+        ACOSS_LAUNCH(kfn, grid, 128, 0, c->stream, A);
+    } else if (packed_ok && c->opt_dp_packed) {
+        auto kfn = k_dp16<CPL>;   // Qmax and Dmax of a cell in one register, DPX s16x2 instructions
         ACOSS_LAUNCH(kfn, grid, 128, 0, c->stream, A);
     } else {
         auto kfn = k_dp<CPL, false>;
@@ -408,9 +414,9 @@ int run_dp_lists(acoss_ctx* c, const ItemLists& L, const uint32_t* d_items_base,
     float* d = c->dout.as<float>();
     float* sw = c->swout.as<float>();
     int rc;
-    if ((rc = launch_dp<4>(c, d_items_base + off4, (int)L.dp4.size(), flags, q, d, sw)) != ACOSS_OK) return rc;
-    if ((rc = launch_dp<8>(c, d_items_base + off8, (int)L.dp8.size(), flags, q, d, sw)) != ACOSS_OK) return rc;
-    if ((rc = launch_dp<16>(c, d_items_base + off16, (int)L.dp16.size(), flags, q, d, sw)) != ACOSS_OK) return rc;
+    if ((rc = launch_dp<4>(c, d_items_base + off4, (int)L.dp4.size(), flags, q, d, sw, L.dp_packed_ok)) != ACOSS_OK) return rc;
+    if ((rc = launch_dp<8>(c, d_items_base + off8, (int)L.dp8.size(), flags, q, d, sw, L.dp_packed_ok)) != ACOSS_OK) return rc;
+    if ((rc = launch_dp<16>(c, d_items_base + off16, (int)L.dp16.size(), flags, q, d, sw, L.dp_packed_ok)) != ACOSS_OK) return rc;
     return ACOSS_OK;
 }
 
@@ -419,7 +425,8 @@ int dp_cpl(const acoss_ctx* c, int cols) {
     return std::min(cpl, c->opt_dp_max_cpl);
 }
 
-void classify_dp(const acoss_ctx* c, ItemLists& L, uint32_t p, int cols) {
+void classify_dp(const acoss_ctx* c, ItemLists& L, uint32_t p, int rows, int cols) {
+    if (rows + cols > kDp16MaxSide) L.dp_packed_ok = false;
     const int cpl = dp_cpl(c, cols);
     (cpl == 4 ? L.dp4 : (cpl == 8 ? L.dp8 : L.dp16)).push_back(p);
 }
@@ -530,7 +537,7 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
                     w.nb_off = nb_total;
                     nb_total += ((int64_t)w.crp_rows * w.nb_stride + 15) & ~(int64_t)15;
                 }
-                classify_dp(c, L, (uint32_t)p, w.crp_cols);
+                classify_dp(c, L, (uint32_t)p, w.crp_rows, w.crp_cols);
                 continue;
             }
             const bool fast_ok = !c->opt_force_wide && (size_t)fast_smem_bytes(32 * kFastBuckets, m, kFastMaxStripRows) <= (size_t)c->max_smem - 1024;
@@ -589,7 +596,7 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
                 }
             }
         }
-        classify_dp(c, L, (uint32_t)p, w.crp_cols);
+        classify_dp(c, L, (uint32_t)p, w.crp_rows, w.crp_cols);
     }
     size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size() +
                      L.t3.size() + L.tsel.size() + L.t1.size() + L.te.size();
@@ -1088,7 +1095,7 @@ int acoss_dp_packed(acoss_ctx* c, const uint32_t* crp, const int64_t* crp_offset
             return fail(ACOSS_ERR_ARG, "plot %d x %d: the DP hand-over packs Qmax values in 16 bits (min side <= 32767)", w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
-        classify_dp(c, L, (uint32_t)b, w.crp_cols);
+        classify_dp(c, L, (uint32_t)b, w.crp_rows, w.crp_cols);
     }
     CU(c->pairs.reserve((size_t)B * sizeof(PairWork)));
     CU(c->crp.reserve((size_t)std::max<int64_t>(crp_total, 1) * sizeof(uint32_t)));
@@ -1171,7 +1178,7 @@ static int align_dense_impl(acoss_ctx* c, const void* csm, int dtype, const int6
             return fail(ACOSS_ERR_ARG, "plot %d x %d: the DP hand-over packs Qmax values in 16 bits (min side <= 32767)", w.crp_rows, w.crp_cols);
         w.bnd_off = br > 0 ? bnd_total : -1;
         bnd_total += br;
-        classify_dp(c, L, (uint32_t)b, w.crp_cols);
+        classify_dp(c, L, (uint32_t)b, w.crp_rows, w.crp_cols);
         el_total += (int64_t)d.rows * d.cols;
         sep_total += (int64_t)d.rows + d.cols;
         crp_total += (int64_t)d.rows * d.wp;
@@ -1526,6 +1533,8 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
         c->opt_single_stream = value ? 1 : 0;
     } else if (n == "debug_flags")
         c->opt_debug_flags = (uint32_t)value;
+    else if (n == "dp_packed")
+        c->opt_dp_packed = value ? 1 : 0;
     else if (n == "dp_max_cpl") {
         if (value != 4 && value != 8 && value != 16) return fail(ACOSS_ERR_ARG, "dp_max_cpl must be 4, 8 or 16");
         c->opt_dp_max_cpl = (int)value;

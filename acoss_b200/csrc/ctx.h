@@ -118,6 +118,7 @@ struct acoss_ctx {
     int opt_force_gscratch = 0;  // ring + strip in global scratch even when shared memory would do
     int opt_dp_max_cpl = 4;      // widest DP kernel used (4, 8, 16).  Measured (profiles/exp/exp_dp_cpl.py):
                                  // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
+    int opt_dp_packed = 1;       // Qmax + Dmax on packed 16-bit lanes (k_dp16) where the plots are small enough; 0: k_dp
     int opt_chunk_pairs = 1 << 18;
     int opt_sweep_gen = 7;         // 7 (default): lane-group selection + packed CRP from the sweep (kernels_sweep7.cuh)
                                    // for every orientation whose column song has <= 1015 frames (m = 9, 12 / 13

@@ -73,6 +73,8 @@ def parse_args():
     ap.add_argument("--all-pairs", action="store_true",
                     help="--impl reference: one step = every unique pair of the set (covers80: 12 720), not a sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
+                    help="library tuning knob for A/B runs (acoss_set_option), e.g. --opt dp_packed=0")
     ap.add_argument("--mfcc", action="store_true", help="also time the default plugin call (chroma + mfcc halves) once")
     ap.add_argument("--full-job", action="store_true", help="score the whole all-pairs matrix once and report its wall time")
     args = ap.parse_args()
@@ -335,6 +337,9 @@ def run_b200(args, rank, world, local):
     ctx = alg._ctx["chroma"][0]
     if args.sweep_gen:
         ctx.set_option("sweep_gen", args.sweep_gen)
+    for kv in args.opt:
+        name, val = kv.split("=", 1)
+        ctx.set_option(name, int(val, 0))
     ts = TileSets(N, lengths, args.pairs_per_step)
     if args.full_job:
         return run_full_job(args, alg, ts, rank, world, barrier)
@@ -616,7 +621,10 @@ def finish_b200(v):
     except Exception:
         pass
     dp_s = stage["dp"] / 1e3
-    int_peak_gcups = N_SM * 128 * sm_max * 1e6 / 4.0 / 1e9   # >= 4 lane-ops per cell update, int32 lanes
+    # integer min / max / add instructions (VIADDMNMX, VIMNMX3, their .S16x2 forms) issue at 64 lanes per clock per SM
+    # on the B200 (profiles/exp/ubench/dpx_rate_b200.txt), half of what SURVEY 8d assumed; the packed kernel spends
+    # 5 of them on a cell's Qmax AND Dmax update, i.e. 2.5 lane-ops per cell update
+    int_peak_gcups = N_SM * 64 * sm_max * 1e6 / 2.5 / 1e9
     dp_gcups = (2.0 * my_q / dp_s / 1e9) if dp_s > 0 else None
     line = {
         "metric": "song_pairs_per_sec", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": steps,
@@ -650,8 +658,10 @@ def finish_b200(v):
                              "the launching stream); traffic = DRAM bytes of the sweep launches for one step's pairs of "
                              "rank 0 (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_sweep_traffic.json)"},
         "roofline_dp": {"bound": "int-alu", "achieved": dp_gcups, "peak": int_peak_gcups, "unit": "GCUPS",
-                        "frac": (dp_gcups / int_peak_gcups) if dp_gcups else None, "kernel": "k_dp<4> (Qmax + Dmax cell updates)",
-                        "note": "peak = 148 SM x 128 int32 lanes x sm_max_mhz / 4 lane-ops per cell update (SURVEY.md 8d)"},
+                        "frac": (dp_gcups / int_peak_gcups) if dp_gcups else None, "kernel": "k_dp16<4> (Qmax + Dmax cell updates on packed s16x2 lanes)",
+                        "note": "peak = 148 SM x 64 integer min/max lanes per clock (measured: profiles/exp/ubench/dpx_rate_b200.txt; "
+                                "SURVEY.md 8d assumed 128) x sm_max_mhz / 2.5 lane-ops per cell update (5 VIADDMNMX.S16x2 per cell for "
+                                "both tables)"},
         "roofline_hbm": {"bound": "hbm", "achieved": (my_bytes / sweep_s / 1e9) if sweep_s > 0 else None, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (my_bytes / sweep_s / 1e9 / hbm_peak) if sweep_s > 0 else None,
                          "note": "compulsory bytes only (both songs' frames + scores); the path is compute-bound by design, "

@@ -223,7 +223,8 @@ int acoss_eval_ranks(acoss_ctx* ctx, const float* D, int64_t n, const int32_t* o
 int acoss_last_eval_ms(acoss_ctx* ctx, float* out);
 
 /* Test / tuning knobs (results never depend on them): "force_wide_sweep" (0/1),
- * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "chunk_pairs" (pairs per internal chunk),
+ * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "dp_packed" (0/1: Qmax + Dmax on packed 16-bit lanes, default 1),
+ * "chunk_pairs" (pairs per internal chunk),
  * "sweep_gen" (2 .. 6: which generation of the cross-similarity sweep runs where it applies;
  * default 6 = FP64 tensor-core sweep for column songs of up to 631 frames, warp-specialised
  * SIMT sweep up to 960, integer-key SIMT sweep up to 1320, general sweeps beyond),

@@ -134,3 +134,28 @@ def test_emu_feature_aggregation(ctx):
         m = np.array(a)
         m[np.isnan(m)] = 0
         assert np.array_equal(got, fo.sync(m, 40, np.mean))
+
+
+def test_emu_dp16_packed_lanes(ctx):
+    """k_dp16 (Qmax + Dmax on packed 16-bit lanes) under emulation: ragged lanes / column blocks, dense plots where the
+    Dmax bonus terms matter, all three lane widths, stale and clean Dmax tables -- against the oracle and against the
+    int32 kernel (dp_packed = 0)."""
+    from oracle import dp
+    rng = np.random.default_rng(78)
+    shapes = [(12, c) for c in (4, 5, 7, 33, 127, 129, 131, 257)] + [(r, 130) for r in (3, 4, 5, 7, 10)] + [(40, 140), (5, 515)]
+    plots = [(rng.uniform(size=(M, N)) < dens).astype(np.uint8) for (M, N) in shapes for dens in (0.08, 0.5, 0.9)]
+    for cpl in (4, 8, 16):
+        ctx.set_option("dp_max_cpl", cpl)
+        try:
+            out = ctx.dp_packed(plots, want_sw=False)
+            outc = ctx.dp_packed(plots, flags=_native.FLAG_DMAX_CLEAN, want_sw=False)
+            ctx.set_option("dp_packed", 0)
+            ref = ctx.dp_packed(plots, want_sw=False)
+        finally:
+            ctx.set_option("dp_max_cpl", 4)
+            ctx.set_option("dp_packed", 1)
+        assert np.array_equal(out[:, :2], ref[:, :2]), cpl
+        for b, B in enumerate(plots):
+            q, d = dp.qmax_dmax_serra09(B)
+            assert (out[b, 0], out[b, 1]) == (q, d), (cpl, B.shape, b % 3)
+            assert outc[b, 1] == dp.dmax_clean(B), (cpl, B.shape, b % 3)
