@@ -293,6 +293,7 @@ def score_tiles(alg, tile_ids, T, tiles=None, lengths=None, place=True):
     lengths = alg.arena_lengths() if lengths is None else lengths
     tiles = tile_list(alg.N, T) if tiles is None else tiles
     sub = [tiles[int(t)] for t in tile_ids]
+    t0 = time.perf_counter()
     shares, load = assign_tiles(tile_costs(lengths, T, sub, alg.m), world)
     mine = tiles_pairs(alg.N, T, [sub[t] for t in shares[rank]])
     t1 = time.perf_counter()
@@ -306,12 +307,14 @@ def score_tiles(alg, tile_ids, T, tiles=None, lengths=None, place=True):
     t2 = time.perf_counter()
     local = np.stack([sims[k].astype(np.float32) for k in keys]) if keys else np.zeros((0, len(mine)), np.float32)
     gathered = gather_score_tiles(local)
+    t3 = time.perf_counter()
     if rank == 0 and place and len(alg.Ds):
         have = [i for i, k in enumerate(keys) if k in alg.Ds]
         place_tiles(alg.Ds, [keys[i] for i in have], alg.N, T, sub, shares, [g[have] for g in gathered])
-    t_gather = time.perf_counter() - t2
+    t4 = time.perf_counter()
     return {"pairs_local": int(len(mine)), "pairs_total": int(sum(tile_pair_count(alg.N, T, t) for t in sub)),
-            "score_s": t_score, "gather_place_s": t_gather, "lpt_imbalance": float(load.max() / max(load.mean(), 1e-30)),
+            "deal_s": t1 - t0, "score_s": t_score, "gather_place_s": t4 - t2, "gather_s": t3 - t2, "place_s": t4 - t3,
+            "lpt_imbalance": float(load.max() / max(load.mean(), 1e-30)),
             "tiles": len(sub), "keys": keys, "pairs_mine": mine}
 
 

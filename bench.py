@@ -379,6 +379,7 @@ def run_b200(args, rank, world, local):
         alg.share_songs_allgather(range(s0, s1))
         parallel.score_tiles(alg, ids, TILE, ts.tiles, lengths)
     share_s = gather_s = 0.0
+    parts = {"deal_s": 0.0, "score_s": 0.0, "gather_s": 0.0, "place_s": 0.0}
     e2e_pairs = 0
     barrier()
     t1 = time.perf_counter()
@@ -388,6 +389,8 @@ def run_b200(args, rank, world, local):
         share_s += time.perf_counter() - ta
         info = parallel.score_tiles(alg, ids, TILE, ts.tiles, lengths)
         gather_s += info["gather_place_s"]
+        for k in parts:
+            parts[k] += info[k]
         e2e_pairs += info["pairs_total"]
     barrier()
     dt_e2e = time.perf_counter() - t1
@@ -561,6 +564,8 @@ def run_full_job(args, alg, ts, rank, world, barrier):
         pairs += info["pairs_total"]
         score_s += info["score_s"]
         gather_s += info["gather_place_s"]
+        for k in parts:
+            parts[k] += info[k]
         imb.append(info["lpt_imbalance"])
     barrier()
     wall = time.perf_counter() - t0
@@ -641,7 +646,8 @@ def finish_b200(v):
         "rank_busy_ms_per_step": {"max": 1e3 * busy_max / steps, "min": 1e3 * float(tmin[0]) / steps},
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": 1e3 * dt_e2e / steps, "share_songs_ms_per_step": 1e3 * share_s / steps,
-                "gather_place_ms_per_step": 1e3 * gather_s / steps},
+                "gather_place_ms_per_step": 1e3 * gather_s / steps,
+                "rank0_ms_per_step": {k[:-2]: 1e3 * x / steps for k, x in v["parts"].items()}},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                      "frac": (achieved_tf / fp64_peak) if achieved_tf else None, "traffic": traffic,
