@@ -58,6 +58,8 @@ SIGNATURES = {
     "acoss_set_option": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64]),
     "acoss_kernel_launches": (ctypes.c_int64, [ctypes.c_void_p]),
     "acoss_reset_counters": (None, [ctypes.c_void_p]),
+    "acoss_bind_score_matrices": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                                 _c_i32p, ctypes.c_int32]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_host_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
@@ -436,6 +438,15 @@ class Context:
 
     def reset_counters(self):
         self.lib.acoss_reset_counters(self._h)
+
+    def bind_score_matrices(self, q_ptr, d_ptr, n, song_of_slot=None):
+        """acoss_bind_score_matrices: q_ptr / d_ptr are DEVICE addresses of n x n float32 matrices (torch tensors'
+        data_ptr(); 0 / None = not wanted, both = unbind); song_of_slot maps uploaded slots to matrix indices."""
+        m = None if song_of_slot is None else np.ascontiguousarray(song_of_slot, dtype=np.int32)
+        rc = self.lib.acoss_bind_score_matrices(self._h, ctypes.c_void_p(int(q_ptr)) if q_ptr else None,
+                                                ctypes.c_void_p(int(d_ptr)) if d_ptr else None, int(n),
+                                                _ptr(m, _c_i32p), 0 if m is None else int(m.size))
+        self._check(rc, "acoss_bind_score_matrices")
 
     def debug_host_ms(self):
         out = np.zeros(6, np.float32)

@@ -147,17 +147,23 @@ class CoverAlgorithm(object):
         (`Ds += Ds.T`), save '<prefix>_Ds.h5'."""
         tic = time.time()
         h5filename = "%s_Ds.h5" % self.get_cacheprefix()
+        self._Ds_dev_valid = False
         if precomputed:
             self.Ds = hdf5io.load(h5filename)
             self.get_all_clique_ids()
         else:
             all_pairs = self.all_pairs_list(symmetric)
+            # the score matrices are also kept on the device where the plugin can (Serra09.device_scores_begin), so
+            # that getEvalStatistics ranks them there without another trip over PCIe
+            on_device = bool(getattr(self, 'device_scores_begin', lambda: False)())
             for p0 in range(0, all_pairs.shape[0], chunk_pairs):
                 self.similarity(all_pairs[p0:p0 + chunk_pairs])
             self.get_all_clique_ids()
             if symmetric:
                 for similarity_type in self.Ds:
                     self.Ds[similarity_type] += self.Ds[similarity_type].T
+            if on_device:
+                self.device_scores_end(symmetric)
             d = os.path.dirname(h5filename)
             if d and not os.path.exists(d):
                 os.makedirs(d)
@@ -254,6 +260,7 @@ class CoverAlgorithm(object):
         """Aggregate batch files into Ds (CoverAlgorithm.py:297-317; the diagonal is counted twice
         there too)."""
         files = glob.glob("{}*.h5".format(fileprefix))
+        self._Ds_dev_valid = False
         for key in self.Ds.keys():
             self.Ds[key] = np.zeros_like(self.Ds[key])
         for f in files:
@@ -288,12 +295,17 @@ class CoverAlgorithm(object):
         """Step 1 + the sort and rank loop of getEvalStatistics (CoverAlgorithm.py:345-382) on the
         device (acoss_eval_ranks, csrc/kernels_eval.cuh): returns (ranks, AllMap) as the reference
         builds them, NaN where the reference leaves NaN."""
-        D = np.ascontiguousarray(self.Ds[similarity_type], dtype=np.float32)
-        N = D.shape[0]
+        N = self.Ds[similarity_type].shape[0]
         if getattr(self, '_eval_ctx', None) is None:
             self._eval_ctx = _native.Context(getattr(self, 'device', 0))
         cliques = [list(self.cliques[s]) for s in self.cliques]
-        iranks, Ks, rows = self._eval_ctx.eval_ranks(D, cliques)
+        dev = (getattr(self, '_Ds_dev', None) or {}).get(similarity_type) if getattr(self, '_Ds_dev_valid', False) else None
+        if dev is not None:
+            # the matrix all_pairwise left on the device (ACOSS_FLAG_DEVICE_INPUT): no 4 N^2-byte upload
+            iranks, Ks, rows = self._eval_ctx.eval_ranks(None, cliques, device_ptr=dev.data_ptr())
+        else:
+            D = np.ascontiguousarray(self.Ds[similarity_type], dtype=np.float32)
+            iranks, Ks, rows = self._eval_ctx.eval_ranks(D, cliques)
         ranks = np.nan * np.ones(N)
         AllMap = np.nan * np.ones(N)
         for i in range(rows):

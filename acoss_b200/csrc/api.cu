@@ -779,6 +779,14 @@ int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, const float* q
     if ((rc = run_dp_lists(c, L, d_items, P.o_dp4, P.o_dp8, P.o_dp16, flags))) return rc;
     CU(cudaEventRecord(c->ev[4], c->stream));
 
+    if (c->bind_q || c->bind_d) {
+        auto ks = k_scatter_scores;
+        ACOSS_LAUNCH(ks, (n + 127) / 128, 128, 0, c->stream, c->pairs.as<PairWork>(), n, c->qout.as<float>(),
+                     c->dout.as<float>(), c->bind_map.p ? c->bind_map.as<int32_t>() : nullptr, c->bind_q, c->bind_d,
+                     c->bind_n);
+        c->launches++;
+        CU(cudaGetLastError());
+    }
     // ---- results
     float* res = reinterpret_cast<float*>(P.stage->as<char>() + P.res_off);
     if (qmax_raw) CU(cudaMemcpyAsync(res, c->qout.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
@@ -904,7 +912,7 @@ int acoss_destroy(acoss_ctx* c) {
                       &c->seps, &c->crp, &c->bnd, &c->qout, &c->dout, &c->swout, &c->otiout, &c->gscratch,
                       &c->dense_in, &c->dense_desc, &c->dense_starts,
                       &c->lens, &c->wnorm, &c->wnmax, &c->sepk, &c->sepx, &c->nb, &c->eval_D, &c->tmat,
-                      &c->frames2, &c->snf_desc, &c->snf_mats, &c->snf_md, &c->snf_sidx, &c->snf_sval};
+                      &c->frames2, &c->snf_desc, &c->snf_mats, &c->snf_md, &c->snf_sidx, &c->snf_sval, &c->bind_map};
     for (DevBuf* b : bufs) b->release();
     c->h_stage.release();
     c->h_stage2.release();
@@ -1069,6 +1077,43 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
     }
     if (pending >= 0 && (rc = deliver(pending))) return rc;
     c->host_ms[0] = ms_since(t_call);
+    return ACOSS_OK;
+}
+
+int acoss_bind_score_matrices(acoss_ctx* c, float* qmax_dev, float* dmax_dev, int64_t n, const int32_t* song_of_slot,
+                              int32_t n_slots) {
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!qmax_dev && !dmax_dev) {   // unbind
+        c->bind_q = c->bind_d = nullptr;
+        c->bind_n = 0;
+        c->bind_map.release();
+        return ACOSS_OK;
+    }
+    if (n <= 0) return fail(ACOSS_ERR_ARG, "score matrices need n > 0");
+#ifndef ACOSS_EMU
+    for (float* p : {qmax_dev, dmax_dev}) {
+        if (!p) continue;
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) != cudaSuccess || at.type != cudaMemoryTypeDevice || at.device != c->device) {
+            cudaGetLastError();
+            return fail(ACOSS_ERR_ARG, "score matrices must be device memory of device %d", c->device);
+        }
+    }
+#endif
+    if (song_of_slot) {
+        if (n_slots <= 0) return fail(ACOSS_ERR_ARG, "song_of_slot needs n_slots > 0");
+        for (int32_t s = 0; s < n_slots; ++s)
+            if (song_of_slot[s] >= n) return fail(ACOSS_ERR_ARG, "song_of_slot[%d] = %d outside the %lld x %lld matrices", s, song_of_slot[s], (long long)n, (long long)n);
+        CU(c->bind_map.reserve((size_t)n_slots * sizeof(int32_t)));
+        CU(cudaMemcpyAsync(c->bind_map.p, song_of_slot, (size_t)n_slots * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    } else {
+        c->bind_map.release();
+    }
+    c->bind_q = qmax_dev;
+    c->bind_d = dmax_dev;
+    c->bind_n = n;
     return ACOSS_OK;
 }
 

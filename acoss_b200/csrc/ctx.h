@@ -111,6 +111,10 @@ struct acoss_ctx {
     DevBuf tmat;                                // tiled long-song sweep: float64 T matrices of the chunk
     DevBuf lens, wnorm, wnmax, sepk, sepx, nb;  // gen-4 sweep: windowed norms, integer separators, nibble CRPs
     int wnorm_m = -1;                           // window the wnorm buffer was computed for
+    float* bind_q = nullptr;   // device-resident score matrices (acoss_bind_score_matrices), not owned
+    float* bind_d = nullptr;
+    int64_t bind_n = 0;
+    DevBuf bind_map;           // song id of every uploaded slot (int32), empty = identity
     PinBuf h_stage, h_stage2;  // pinned staging images of two consecutive chunks
     std::vector<uint32_t> h_crp;
     // test/tuning knobs (acoss_set_option)

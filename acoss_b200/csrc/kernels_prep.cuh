@@ -76,4 +76,23 @@ __global__ void __launch_bounds__(128) k_oti(PairWork* __restrict__ pairs, int n
     pairs[p].oti = best;
 }
 
+// Scores of a chunk into device-resident N x N score matrices (acoss_bind_score_matrices): what Serra09.similarity
+// stores, raw / (M + N) (Serra09.py:174-175), computed like the host does (float64 division, rounded to the matrices'
+// float32) and written at [row][col] = (song id of the pair's first song, of its second).  One thread per pair.
+__global__ void __launch_bounds__(128) k_scatter_scores(const PairWork* __restrict__ pairs, int n_pairs,
+                                                        const float* __restrict__ qraw, const float* __restrict__ draw,
+                                                        const int32_t* __restrict__ song_of_slot, float* __restrict__ Dq,
+                                                        float* __restrict__ Dd, int64_t n) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pairs) return;
+    const PairWork w = pairs[p];
+    const int64_t i = song_of_slot ? song_of_slot[w.song_i] : w.song_i;
+    const int64_t j = song_of_slot ? song_of_slot[w.song_j] : w.song_j;
+    if (i < 0 || j < 0 || i >= n || j >= n) return;
+    double mn = (double)(w.M + w.N);
+    if (mn <= 0.0) mn = 1.0;
+    if (Dq) Dq[i * n + j] = (float)((double)qraw[p] / mn);
+    if (Dd) Dd[i * n + j] = (float)((double)draw[p] / mn);
+}
+
 }  // namespace acoss

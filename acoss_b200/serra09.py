@@ -259,6 +259,8 @@ class Serra09(CoverAlgorithm):
         for kind, flags in kinds:
             ctx, slot = self._context_for(kind, idxs.reshape(-1))
             pairs = slot[idxs].astype(np.int32)
+            if getattr(self, '_Ds_dev', None) is not None and not self._Ds_dev_valid:
+                self._bind_device_scores(kind, ctx, slot)
             r = ctx.serra09_pairs(pairs, m=self.m, kappa=self.kappa, flags=flags)
             MN = r['shape'].sum(axis=1).astype(np.float64)     # M + N (Serra09.py:174-175)
             MN[MN <= 0] = 1.0
@@ -271,6 +273,50 @@ class Serra09(CoverAlgorithm):
                 if key in self.Ds:
                     self.Ds[key][idxs[:, 0], idxs[:, 1]] = similarities[key]
         return similarities
+
+    # ------------------------------------------------------------------ device-resident score matrices
+    def device_scores_begin(self):
+        """Keep the N x N score matrices on the device as well (acoss_bind_score_matrices): every similarity() call
+        scatters its normalised scores into them next to returning them, all_pairwise symmetrises them there, and
+        getEvalStatistics ranks them without the N x N matrix crossing PCIe.  Returns False (and does nothing) when
+        there is no CUDA torch, the subclass scores differently (ChenFusion, EarlySNF) or the matrices would not fit."""
+        if type(self).similarity is not Serra09.similarity:
+            return False
+        try:
+            import torch
+        except ImportError:
+            return False
+        if not torch.cuda.is_available() or self.N * self.N * 4 * len(self.similarity_types) > (16 << 30):
+            return False
+        dev = torch.device('cuda', self.device)
+        self._Ds_dev = {k: torch.zeros((self.N, self.N), dtype=torch.float32, device=dev) for k in self.similarity_types}
+        self._Ds_dev_bound = {}
+        self._Ds_dev_valid = False
+        return True
+
+    def device_scores_end(self, symmetric):
+        """all_pairwise is through: `Ds += Ds.T` on the device copies (CoverAlgorithm.py:180-182), mark them usable."""
+        import torch
+        for key, t in self._Ds_dev.items():
+            if symmetric:
+                t.copy_(t + t.t())
+        torch.cuda.synchronize(self.device)
+        for ctx, _ in self._ctx.values():
+            ctx.bind_score_matrices(0, 0, 0)
+        self._Ds_dev_bound = {}
+        self._Ds_dev_valid = True
+
+    def _bind_device_scores(self, kind, ctx, slot):
+        gen = (id(ctx), getattr(self, '_upload_gen', 0))
+        if self._Ds_dev_bound.get(kind) == gen:
+            return
+        used = np.nonzero(slot >= 0)[0]
+        song_of_slot = -np.ones(int(slot[used].max()) + 1 if used.size else 1, dtype=np.int32)
+        song_of_slot[slot[used]] = used
+        q, d = self._Ds_dev.get('%s_qmax' % kind), self._Ds_dev.get('%s_dmax' % kind)
+        ctx.bind_score_matrices(q.data_ptr() if q is not None else 0, d.data_ptr() if d is not None else 0, self.N,
+                                song_of_slot)
+        self._Ds_dev_bound[kind] = gen
 
     def drop_device_arena(self):
         """Forget what is resident on the device (the host-side feature cache stays): the next
@@ -289,6 +335,8 @@ class Serra09(CoverAlgorithm):
         for ctx, _ in self._ctx.values():
             ctx.close()
         self._ctx = {}
+        self._Ds_dev = None
+        self._Ds_dev_valid = False
         if self._feat_ctx is not None:
             self._feat_ctx.close()
             self._feat_ctx = None

@@ -222,6 +222,19 @@ int acoss_eval_ranks(acoss_ctx* ctx, const float* D, int64_t n, const int32_t* o
 /* Device time (ms) of the k_eval_ranks launch of the last acoss_eval_ranks call. */
 int acoss_last_eval_ms(acoss_ctx* ctx, float* out);
 
+/*
+ * Device-resident score matrices: after this call every acoss_serra09_pairs on the context ALSO writes, for each pair
+ * (a, b) of its list, qmax_raw / (M + N) and dmax_raw / (M + N) -- what Serra09.similarity stores in
+ * self.Ds[...][i][j] (benchmarking/Serra09.py:174-175; float64 division rounded to float32) -- to
+ * qmax_dev[i * n + j] / dmax_dev[i * n + j], i = song_of_slot[a], j = song_of_slot[b] (identity when song_of_slot is
+ * NULL; negative entries are skipped).  The matrices are the caller's device memory (n x n float32, e.g. torch tensors)
+ * and stay the caller's; CoverAlgorithm.all_pairwise symmetrises them on the device and getEvalStatistics hands them to
+ * acoss_eval_ranks with ACOSS_FLAG_DEVICE_INPUT, so the N x N matrix never crosses PCIe for the evaluation
+ * (benchmarking/CoverAlgorithm.py:166-183, 345-382).  Either pointer may be NULL; both NULL unbinds.
+ */
+int acoss_bind_score_matrices(acoss_ctx* ctx, float* qmax_dev, float* dmax_dev, int64_t n, const int32_t* song_of_slot,
+                              int32_t n_slots);
+
 /* Test / tuning knobs (results never depend on them): "force_wide_sweep" (0/1),
  * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "dp_packed" (0/1: Qmax + Dmax on packed 16-bit lanes, default 1),
  * "chunk_pairs" (pairs per internal chunk),

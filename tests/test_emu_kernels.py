@@ -159,3 +159,29 @@ def test_emu_dp16_packed_lanes(ctx):
             q, d = dp.qmax_dmax_serra09(B)
             assert (out[b, 0], out[b, 1]) == (q, d), (cpl, B.shape, b % 3)
             assert outc[b, 1] == dp.dmax_clean(B), (cpl, B.shape, b % 3)
+
+
+def test_emu_bound_score_matrices(ctx):
+    """acoss_bind_score_matrices under emulation ("device" memory is host memory there): the scores of a call land at
+    [song of slot a][song of slot b] as raw / (M + N) rounded to float32, other cells stay untouched."""
+    songs, _ = synth.make_song_set("covers80", seed=23, n_songs=5, length_range=(30, 60))
+    ctx.upload_songs(songs)
+    n = 9
+    song_of_slot = np.array([7, 2, 5, 0, 3], np.int32)
+    Dq = np.full((n, n), -1.0, np.float32)
+    Dd = np.full((n, n), -1.0, np.float32)
+    pairs = np.array([(0, 1), (1, 2), (3, 4), (4, 0)], np.int32)
+    ctx.bind_score_matrices(Dq.ctypes.data, Dd.ctypes.data, n, song_of_slot)
+    try:
+        r = ctx.serra09_pairs(pairs, m=5, kappa=0.1)
+    finally:
+        ctx.bind_score_matrices(0, 0, 0)
+    want_q = np.full((n, n), -1.0, np.float32)
+    want_d = np.full((n, n), -1.0, np.float32)
+    for p, (a, b) in enumerate(pairs):
+        mn = float(r["shape"][p].sum())
+        want_q[song_of_slot[a], song_of_slot[b]] = np.float32(np.float64(r["qmax_raw"][p]) / mn)
+        want_d[song_of_slot[a], song_of_slot[b]] = np.float32(np.float64(r["dmax_raw"][p]) / mn)
+    assert np.array_equal(Dq, want_q) and np.array_equal(Dd, want_d)
+    again = ctx.serra09_pairs(pairs, m=5, kappa=0.1)   # unbound: nothing is written any more
+    assert np.array_equal(again["qmax_raw"], r["qmax_raw"]) and np.array_equal(Dq, want_q)

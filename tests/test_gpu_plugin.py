@@ -29,7 +29,16 @@ def test_all_pairwise_matches_oracle_and_writes_artefacts(tmp_path, monkeypatch)
     from scipy.io import loadmat
     mat = loadmat("cache/Serra09_t24_Ds.mat")
     assert mat["chroma_qmax"].dtype == np.float32 and np.array_equal(mat["chroma_dmax"], ref["chroma_dmax"])
+    # the score matrices all_pairwise left on the device are the host ones, bit for bit, and getEvalStatistics ranks
+    # them there (no N x N upload) with the same result as through the host matrix
+    assert alg._Ds_dev_valid
+    for key in ("chroma_qmax", "chroma_dmax"):
+        assert np.array_equal(alg._Ds_dev[key].cpu().numpy(), ref[key]), key
     MR, MRR, MDR, MAP, tops = alg.getEvalStatistics("chroma_qmax")
+    alg._Ds_dev_valid = False
+    host = alg.getEvalStatistics("chroma_qmax")
+    alg._Ds_dev_valid = True
+    assert (MR, MRR, MDR, MAP) == host[:4] and np.array_equal(tops, host[4])
     assert 0 < MAP <= 1 and MR >= 1
     # covers are recognisable in the synthetic set: the mate of most songs ranks first
     assert tops[0] >= 12
