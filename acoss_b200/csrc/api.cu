@@ -48,6 +48,7 @@ constexpr int64_t kMaxChunkNbBytes = (int64_t)6 << 30;     // 6 GiB of nibble-by
 constexpr int64_t kMaxWaveTmatDoubles = (int64_t)4 << 30;  // 32 GiB of T matrices per wave of the tiled long-song sweep
 constexpr int kCounterSlots = 96;
 constexpr int kG6Buckets = kS6Buckets;  // gen-6 launch buckets: CTAs of 128, 256, 512, 640 threads
+constexpr int kG4Buckets = kS4MaxWarps;            // gen-4 sweep: bucket b = b + 1 warps
 constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) threads, up to 128 * (b + 1) columns
 
 struct ItemLists {
@@ -60,7 +61,7 @@ struct ItemLists {
     std::vector<size_t> wave_t3, wave_tsel, wave_te;                 // first item of every wave in t3 / tsel / te
     std::vector<uint32_t> te;                                        // pairs whose CRP comes from the stored T matrix
     int te_rows = 0;
-    std::vector<uint32_t> g4_0[kFastBuckets], g4_2[kFastBuckets];    // gen-4 sweep: separators / CRP
+    std::vector<uint32_t> g4_0[kG4Buckets], g4_2[kG4Buckets];    // gen-4 sweep: separators / CRP
     std::vector<uint32_t> g6_0[kS6Buckets], g6_2[kS6Buckets];  // gen-6 (DMMA) sweep by CTA size
     std::vector<uint32_t> g5_0[2], g5_2[2];                          // gen-5 sweep, 4 / 8 compute warps
     std::vector<uint32_t> g4_pack;                                   // pairs whose nibble CRP needs packing
@@ -82,7 +83,7 @@ struct ChunkPlan {
     size_t n_items = 0, pw_bytes = 0, res_off = 0;   // res_off: float results [q | d | sw] of n each in the staging image
     PinBuf* stage = nullptr;
     size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16;
-    size_t o_g40[kFastBuckets], o_g42[kFastBuckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
+    size_t o_g40[kG4Buckets], o_g42[kG4Buckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
     size_t o_g70[kSweep7Buckets], o_g72[kSweep7Buckets], o_t3, o_tsel, o_t1, o_te;
 };
 
@@ -451,7 +452,7 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
     const bool tiled_ok = c->opt_tiled_wide && !c->opt_force_gscratch && tile_stride(m) >= 32 &&
                           tile_smem_bytes(m, BINS) <= (size_t)c->max_smem - 1024 && n < (1 << (kTileItemBits - 1));
     const bool gen4_ok = c->opt_sweep_gen >= 4 && BINS == 12 && !c->opt_force_wide && s4_own_lanes(m) >= 16 &&
-                         (size_t)s4_layout(32 * kFastBuckets, m, BINS).total <= (size_t)c->max_smem - 1024;
+                         (size_t)s4_layout(32 * kG4Buckets, m, BINS).total <= (size_t)c->max_smem - 1024;
     const bool g7_ok = c->opt_sweep_gen >= 7 && m == 9 && (BINS == 12 || BINS == 13) && !c->opt_force_wide;
     const bool noswap = (flags & kFlagNoSwap) != 0;
     const bool nonmutual = (flags & kFlagNonMutual) != 0;
@@ -600,8 +601,8 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
     }
     size_t n_items = L.wide0.size() + L.wide1.size() + L.dp4.size() + L.dp8.size() + L.dp16.size() + L.g4_pack.size() +
                      L.t3.size() + L.tsel.size() + L.t1.size() + L.te.size();
-    for (int b = 0; b < kFastBuckets; ++b)
-        n_items += L.fast0[b].size() + L.fast2[b].size() + L.g4_0[b].size() + L.g4_2[b].size();
+    for (int b = 0; b < kFastBuckets; ++b) n_items += L.fast0[b].size() + L.fast2[b].size();
+    for (int b = 0; b < kG4Buckets; ++b) n_items += L.g4_0[b].size() + L.g4_2[b].size();
     for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
     for (int b = 0; b < kG6Buckets; ++b) n_items += L.g6_0[b].size() + L.g6_2[b].size();
     for (int b = 0; b < kSweep7Buckets; ++b) n_items += L.g7_0[b].size() + L.g7_2[b].size();
@@ -632,8 +633,8 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
     P.o_dp4 = put(L.dp4);
     P.o_dp8 = put(L.dp8);
     P.o_dp16 = put(L.dp16);
-    for (int b = 0; b < kFastBuckets; ++b) P.o_g40[b] = put(L.g4_0[b]);
-    for (int b = 0; b < kFastBuckets; ++b) P.o_g42[b] = put(L.g4_2[b]);
+    for (int b = 0; b < kG4Buckets; ++b) P.o_g40[b] = put(L.g4_0[b]);
+    for (int b = 0; b < kG4Buckets; ++b) P.o_g42[b] = put(L.g4_2[b]);
     P.o_g4pack = put(L.g4_pack);
     for (int b = 0; b < 2; ++b) P.o_g50[b] = put(L.g5_0[b]);
     for (int b = 0; b < 2; ++b) P.o_g52[b] = put(L.g5_2[b]);
@@ -756,7 +757,7 @@ int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, const float* q
         if (BINS == 12 && (rc = launch_sweep6<0>(c, d_items + P.o_g60[b], (int)L.g6_0[b].size(), b, m, d_cnt + 64 + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep5<0>(c, d_items + P.o_g50[b], (int)L.g5_0[b].size(), b + 1, m, d_cnt + 56 + b, flags))) return rc;
-    for (int b = kFastBuckets - 1; b >= 0; --b)
+    for (int b = kG4Buckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + P.o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
     for (int b = kSweep7Buckets - 1; b >= 0; --b)
@@ -765,8 +766,8 @@ int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, const float* q
         if (BINS == 12 && (rc = launch_sweep6<2>(c, d_items + P.o_g62[b], (int)L.g6_2[b].size(), b, m, d_cnt + 64 + kG6Buckets + b, flags))) return rc;
     for (int b = 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep5<2>(c, d_items + P.o_g52[b], (int)L.g5_2[b].size(), b + 1, m, d_cnt + 58 + b, flags))) return rc;
-    for (int b = kFastBuckets - 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep4<12, 2>(c, d_items + P.o_g42[b], (int)L.g4_2[b].size(), b, m, d_cnt + 32 + kFastBuckets + b, flags))) return rc;
+    for (int b = kG4Buckets - 1; b >= 0; --b)
+        if (BINS == 12 && (rc = launch_sweep4<12, 2>(c, d_items + P.o_g42[b], (int)L.g4_2[b].size(), b, m, d_cnt + 32 + kG4Buckets + b, flags))) return rc;
     if (!L.g4_pack.empty()) {
         auto kp = k_nb_to_packed;
         ACOSS_LAUNCH(kp, (int)L.g4_pack.size(), 128, 0, c->stream, c->pairs.as<PairWork>(), d_items + P.o_g4pack,

@@ -51,7 +51,7 @@ static __device__ unsigned long long g_s4_sel_stats[8];
 #endif
 
 constexpr int kS4Stage = 32;        // rows of the row song per TMA bulk copy
-constexpr int kS4MaxWarps = 11;     // CTAs of up to 352 threads
+constexpr int kS4MaxWarps = 11;     // CTAs of up to 352 threads (12 warps fit, measured no faster: profiles/exp/README_r02.md)
 constexpr int kS4EMax = 6;          // ranks walked by the extraction pass
 constexpr int kS4MaxFlag = 32;      // flagged columns / patch candidates kept per item / row
 constexpr int32_t kKeyInf = 0x7fffffff;
