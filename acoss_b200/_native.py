@@ -62,6 +62,7 @@ SIGNATURES = {
                                                  _c_i32p, ctypes.c_int32]),
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_host_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
+    "acoss_last_aggregate_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]),
     "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
     "acoss_upload_aux_songs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int32]),
     "acoss_snf_pairs": (ctypes.c_int, [ctypes.c_void_p, _c_i32p, ctypes.c_int64, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
@@ -327,6 +328,30 @@ class Context:
         ("frames_x_bins": hpcp / crema) or all (bins, n) ("bins_x_frames": mfcc_htk).  Returns a
         list of (bins, ceil(n / fac)) arrays like librosa.util.sync(a.T or a, arange(0, n, fac))
         and, with want_gchroma, the (n_songs, bins) global chroma (Serra09.py:24-28)."""
+        # groups of at most 256 MB of input: the page-locked staging buffers stay small and are allocated once
+        budget, groups, cur, size = 256 << 20, [], [], 0
+        for a in arrays:
+            nb = int(np.asarray(a).size) * 8
+            if cur and size + nb > budget:
+                groups.append(cur)
+                cur, size = [], 0
+            cur.append(a)
+            size += nb
+        if len(groups) >= 1:
+            groups.append(cur)
+            res, gs, ms, nbytes = [], [], 0.0, 0.0
+            for grp in groups:
+                r = self.aggregate_songs(grp, fac, aggregate, layout, zero_nonfinite, want_gchroma)
+                res += r[0] if want_gchroma else r
+                if want_gchroma:
+                    gs.append(r[1])
+                a, b = self.last_aggregate_stats()
+                ms, nbytes = ms + a, nbytes + b
+            self._agg_stats = (ms, nbytes)
+            if want_gchroma:
+                dt = np.float64 if any(g.dtype == np.float64 for g in gs) else np.float32
+                return res, np.concatenate([g.astype(dt) for g in gs], axis=0)
+            return res
         S = len(arrays)
         dt = np.float64 if any(np.asarray(a).dtype == np.float64 for a in arrays) else np.float32
         lay = 0 if layout == "frames_x_bins" else 1
@@ -335,7 +360,9 @@ class Context:
         offs = np.zeros(S, np.int64)
         if S > 1:
             offs[1:] = np.cumsum(nfr[:-1].astype(np.int64))
-        flat = np.empty(max(int(nfr.astype(np.int64).sum()) * max(bins, 1), 1), dt)
+        # staging buffers in page-locked memory, kept by the context and grown as needed (allocating them costs more
+        # than the copy): the library then moves a chunk with one asynchronous copy at PCIe speed
+        flat = self._staging("in", max(int(nfr.astype(np.int64).sum()) * max(bins, 1), 1), dt)
         for a, o, n in zip(arrays, offs, nfr):
             a = np.ascontiguousarray(a, dtype=dt)
             if a.shape[1 if lay == 0 else 0] != bins:
@@ -345,7 +372,7 @@ class Context:
         ooffs = np.zeros(S, np.int64)
         if S > 1:
             ooffs[1:] = np.cumsum(L[:-1])
-        out = np.empty(max(int(L.sum()) * max(bins, 1), 1), dt)
+        out = self._staging("out", max(int(L.sum()) * max(bins, 1), 1), dt)
         g = np.empty((S, bins), dt) if want_gchroma else None
         rc = self.lib.acoss_aggregate_songs(self._h, flat.ctypes.data_as(ctypes.c_void_p), F64 if dt == np.float64 else F32,
                                             lay, _ptr(offs, _c_i64p), _ptr(nfr, _c_i32p), S, bins, int(fac),
@@ -353,8 +380,28 @@ class Context:
                                             out.ctypes.data_as(ctypes.c_void_p), _ptr(ooffs, _c_i64p),
                                             None if g is None else g.ctypes.data_as(ctypes.c_void_p))
         self._check(rc, "acoss_aggregate_songs")
-        res = [out[o * bins:(o + int(l)) * bins].reshape(int(l), bins).T for o, l in zip(ooffs, L)]
+        res = [np.array(out[o * bins:(o + int(l)) * bins].reshape(int(l), bins).T) for o, l in zip(ooffs, L)]   # copies: `out` is reused
         return (res, g) if want_gchroma else res
+
+    def last_aggregate_stats(self):
+        """(device ms of the aggregation kernel launches, bytes they moved) of the last aggregate_songs call."""
+        if getattr(self, "_agg_stats", None) is not None:
+            st, self._agg_stats = self._agg_stats, None
+            return st
+        out = np.zeros(2, np.float64)
+        self._check(self.lib.acoss_last_aggregate_stats(self._h, out.ctypes.data_as(ctypes.POINTER(ctypes.c_double))),
+                    "acoss_last_aggregate_stats")
+        return float(out[0]), float(out[1])
+
+    def _staging(self, which, n, dtype):
+        """First n elements (as dtype) of a page-locked byte buffer owned by this context."""
+        need = int(n) * np.dtype(dtype).itemsize
+        bufs = self.__dict__.setdefault("_stage_bufs", {})
+        buf = bufs.get(which)
+        if buf is None or buf.nbytes < need:
+            buf = _host_array((max(need + need // 4, 1 << 20),), np.uint8, pinned=True)
+            bufs[which] = buf
+        return buf[:need].view(dtype)
 
     def eval_ranks(self, D, cliques, device_ptr=None):
         """The rank loop of CoverAlgorithm.getEvalStatistics (CoverAlgorithm.py:345-382) on the device.

@@ -1376,6 +1376,8 @@ int acoss_aggregate_songs(acoss_ctx* c, const void* full, int dtype, int layout,
     for (int s = 0; s < n_songs; ++s)
         if (nframes[s] < 1) return fail(ACOSS_ERR_ARG, "song %d has no frames", s);
     CU(cudaSetDevice(c->device));
+    c->feat_kernel_ms = 0.f;
+    c->feat_bytes = 0.0;
     const size_t es = dtype == ACOSS_F32 ? 4 : 8;
     const size_t chunk_budget = (size_t)512 << 20;  // bytes of full-rate input per chunk
     DevBuf d_in, d_out, d_meta, d_g;
@@ -1405,13 +1407,21 @@ int acoss_aggregate_songs(acoss_ctx* c, const void* full, int dtype, int layout,
         CU(d_out.reserve(out_el * es));
         CU(d_meta.reserve((size_t)ns * (2 * sizeof(int64_t) + sizeof(int32_t)) + 64));
         if (gchroma_out) CU(d_g.reserve((size_t)ns * bins * es));
-        // songs need not be contiguous on the host: one copy per song
+        // songs need not be contiguous on the host: one copy per song, unless they are (one copy per chunk)
         int maxL = 0;
+        bool packed = true;
         for (int s = s0; s < s1; ++s) {
-            CU(cudaMemcpyAsync(d_in.as<char>() + (size_t)in_off[s - s0] * es,
-                               reinterpret_cast<const char*>(full) + (size_t)offsets[s] * bins * es,
-                               (size_t)nframes[s] * bins * es, cudaMemcpyHostToDevice, c->stream));
+            packed = packed && (offsets[s] - offsets[s0]) * (int64_t)bins == in_off[s - s0];
             maxL = std::max(maxL, (nframes[s] + fac - 1) / fac);
+        }
+        if (packed) {
+            CU(cudaMemcpyAsync(d_in.p, reinterpret_cast<const char*>(full) + (size_t)offsets[s0] * bins * es, in_el * es,
+                               cudaMemcpyHostToDevice, c->stream));
+        } else {
+            for (int s = s0; s < s1; ++s)
+                CU(cudaMemcpyAsync(d_in.as<char>() + (size_t)in_off[s - s0] * es,
+                                   reinterpret_cast<const char*>(full) + (size_t)offsets[s] * bins * es,
+                                   (size_t)nframes[s] * bins * es, cudaMemcpyHostToDevice, c->stream));
         }
         int64_t* m_in = d_meta.as<int64_t>();
         int64_t* m_out = m_in + ns;
@@ -1436,6 +1446,7 @@ int acoss_aggregate_songs(acoss_ctx* c, const void* full, int dtype, int layout,
         const int64_t grid64 = (int64_t)A.blocks_per_song * ns;
         if (grid64 > 0x7fffffffLL) return fail(ACOSS_ERR_ARG, "aggregation chunk too large");
         const int grid = (int)grid64;
+        CU(cudaEventRecord(c->ev[0], c->stream));
         if (dtype == ACOSS_F32) {
             auto kf = k_feat_aggregate<float>;
             ACOSS_LAUNCH(kf, grid, 128, 0, c->stream, A);
@@ -1443,6 +1454,7 @@ int acoss_aggregate_songs(acoss_ctx* c, const void* full, int dtype, int layout,
             auto kf = k_feat_aggregate<double>;
             ACOSS_LAUNCH(kf, grid, 128, 0, c->stream, A);
         }
+        CU(cudaEventRecord(c->ev[1], c->stream));
         c->launches++;
         CU(cudaGetLastError());
         if (gchroma_out) {
@@ -1458,13 +1470,27 @@ int acoss_aggregate_songs(acoss_ctx* c, const void* full, int dtype, int layout,
             CU(cudaMemcpyAsync(reinterpret_cast<char*>(gchroma_out) + (size_t)s0 * bins * es, d_g.p, (size_t)ns * bins * es,
                                cudaMemcpyDeviceToHost, c->stream));
         }
-        for (int s = s0; s < s1; ++s) {
-            const size_t L = (size_t)((nframes[s] + fac - 1) / fac);
-            CU(cudaMemcpyAsync(reinterpret_cast<char*>(out) + (size_t)out_offsets[s] * bins * es,
-                               d_out.as<char>() + (size_t)out_off[s - s0] * es, L * bins * es, cudaMemcpyDeviceToHost,
-                               c->stream));
+        bool packed_out = true;
+        for (int s = s0; s < s1; ++s)
+            packed_out = packed_out && (out_offsets[s] - out_offsets[s0]) * (int64_t)bins == out_off[s - s0];
+        if (packed_out) {
+            CU(cudaMemcpyAsync(reinterpret_cast<char*>(out) + (size_t)out_offsets[s0] * bins * es, d_out.p, out_el * es,
+                               cudaMemcpyDeviceToHost, c->stream));
+        } else {
+            for (int s = s0; s < s1; ++s) {
+                const size_t L = (size_t)((nframes[s] + fac - 1) / fac);
+                CU(cudaMemcpyAsync(reinterpret_cast<char*>(out) + (size_t)out_offsets[s] * bins * es,
+                                   d_out.as<char>() + (size_t)out_off[s - s0] * es, L * bins * es, cudaMemcpyDeviceToHost,
+                                   c->stream));
+            }
         }
         CU(cudaStreamSynchronize(c->stream));
+        {
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+            c->feat_kernel_ms += ms;
+            c->feat_bytes += (double)(in_el + out_el) * es;
+        }
         s0 = s1;
     }
     return ACOSS_OK;
@@ -1626,6 +1652,13 @@ int acoss_debug_sweep7_stats(acoss_ctx* c, uint64_t out[16], int reset) {
     const int rc = acoss_sweep7_stats(c, h, reset);
     for (int i = 0; i < 16; ++i) out[i] = h[i];
     return rc;
+}
+
+int acoss_last_aggregate_stats(acoss_ctx* c, double out[2]) {
+    if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
+    out[0] = c->feat_kernel_ms;
+    out[1] = c->feat_bytes;
+    return ACOSS_OK;
 }
 
 int acoss_debug_host_ms(acoss_ctx* c, float out[6]) {

@@ -142,6 +142,8 @@ struct acoss_ctx {
     // accounting
     int64_t launches = 0;
     float stage_ms[5] = {0, 0, 0, 0, 0};
+    float feat_kernel_ms = 0.f;   // k_feat_aggregate launches of the last acoss_aggregate_songs call (CUDA events)
+    double feat_bytes = 0.0;      // bytes they read + wrote
     float host_ms[6] = {0, 0, 0, 0, 0, 0};  // host wall times of the last acoss_serra09_pairs call (acoss_debug_host_ms)
     bool have_stage_ms = false;
     float eval_ms = -1.f;  // device time of the last k_eval_ranks launch

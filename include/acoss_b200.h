@@ -258,6 +258,10 @@ int acoss_debug_sweep6_cycles(acoss_ctx* ctx, uint64_t out[8], int reset);
  * built with -DACOSS_S7_STATS. */
 int acoss_debug_sweep7_stats(acoss_ctx* ctx, uint64_t out[16], int reset);
 
+/* Measurement aid: out[0] = device time (ms, CUDA events) of the k_feat_aggregate launches of the last
+ * acoss_aggregate_songs call, out[1] = the bytes they read and wrote (full-rate input + aggregated output). */
+int acoss_last_aggregate_stats(acoss_ctx* ctx, double out[2]);
+
 /* Profiling aid: host wall times (ms) of the last acoss_serra09_pairs call: [0] whole call, [1] preparing the first
  * chunk (not overlapped), [2] issuing copies + launches, [3] preparing chunks 2.. and handing out earlier results (overlapped with kernels),
  * [4] waiting for the stream, [5] handing results out (mostly inside [3]). */
