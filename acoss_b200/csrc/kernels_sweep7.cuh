@@ -498,6 +498,10 @@ __global__ void __launch_bounds__(NT, (S7Cfg<NT, CPT>::MINB)) k_sweep7(Sweep7Arg
                         if (have_prev) {
                             // the previous row's separator, extrapolated by half the last step (absolute key units)
                             t0 = prev_abs + (have_prev2 ? (prev_abs - prev2_abs) / 2 : 0) - kwx;
+                        } else if ((A.flags & (1u << 22)) && sp_idx > 0) {
+                            // A/B (debug flag): first row of the chain from the last row of the previous strip
+                            // (w RPW + 1 rows back) instead of the order-statistic estimate of its own keys
+                            t0 = misc[10 + ((sp_idx - 1) & 1)] - kwx;
                         } else {
                             t0 = s4_estimate(keys, est_rank, lane);   // first row of the chain: from its own keys
                             have_g = t0 < kKeyInf - 1;
@@ -536,6 +540,7 @@ __global__ void __launch_bounds__(NT, (S7Cfg<NT, CPT>::MINB)) k_sweep7(Sweep7Arg
 #endif
                         }
                         if (lane == 0) rthr[srow] = thr;
+                        if (srow == s_last && lane == 0) misc[10 + (sp_idx & 1)] = prev_abs;
                         have_prev = true;
 #if ACOSS_S7_STAT
                         if (lane == 0) atomicAdd(&g_s7_stats[0], 1ull);
