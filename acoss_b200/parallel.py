@@ -237,9 +237,11 @@ def tile_pair_count(n_songs, T, tile):
 
 
 # ---------------------------------------------------------------------------- scores: float32 tiles to rank 0
-def gather_score_tiles(local, dst=0, device=None):
+def gather_score_tiles(local, dst=0, device=None, counts=None, timing=None):
     """local: float32 array [n_types, n_local_pairs] of this rank (pairs in the order of its tile list).
-    Returns on `dst` a list of per-rank [n_types, n_pairs_of_rank] arrays, None elsewhere.  Single process: [local]."""
+    Returns on `dst` a list of per-rank [n_types, n_pairs_of_rank] arrays, None elsewhere.  Single process: [local].
+    counts: every rank's pair count when the caller knows them (the tile deal is deterministic), which saves a
+    collective; timing: dict that receives the seconds spent waiting for / receiving the other ranks' buffers."""
     import torch
     import torch.distributed as dist
     local = np.ascontiguousarray(local, dtype=np.float32)
@@ -249,16 +251,27 @@ def gather_score_tiles(local, dst=0, device=None):
     if device is None:
         device = _default_device()
     K = local.shape[0]
-    n = torch.tensor([local.shape[1]], dtype=torch.int64, device=device)
-    counts = _allgather(n).view(-1).cpu().numpy()
+    if counts is None:
+        n = torch.tensor([local.shape[1]], dtype=torch.int64, device=device)
+        counts = _allgather(n).view(-1).cpu().numpy()
+    counts = np.asarray(counts, dtype=np.int64)
+    assert int(counts[rank]) == local.shape[1], "rank %d: %d scores for %d pairs" % (rank, local.shape[1], counts[rank])
     nmax = int(counts.max())
+    t0 = time.perf_counter()
     buf = torch.zeros((K, max(nmax, 1)), dtype=torch.float32, device=device)
     buf[:, :local.shape[1]] = torch.from_numpy(local).to(device)
     outs = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
     dist.gather(buf, gather_list=outs, dst=dst)
     if rank != dst:
         return None
-    return [o[:, :int(c)].cpu().numpy() for o, c in zip(outs, counts)]
+    if torch.device(device).type == 'cuda':
+        torch.cuda.synchronize(device)
+    t1 = time.perf_counter()
+    host = torch.stack(outs).cpu().numpy()          # one device-to-host copy for all ranks
+    if timing is not None:
+        timing["gather_wait_s"] = t1 - t0
+        timing["gather_d2h_s"] = time.perf_counter() - t1
+    return [host[r][:, :int(c)] for r, c in enumerate(counts)]
 
 
 def place_tiles(Ds, keys, n_songs, T, tiles, shares, per_rank_scores):
@@ -306,7 +319,9 @@ def score_tiles(alg, tile_ids, T, tiles=None, lengths=None, place=True):
     keys = sorted(sims.keys())
     t2 = time.perf_counter()
     local = np.stack([sims[k].astype(np.float32) for k in keys]) if keys else np.zeros((0, len(mine)), np.float32)
-    gathered = gather_score_tiles(local)
+    timing = {}
+    counts = [sum(tile_pair_count(alg.N, T, sub[t]) for t in shares[r]) for r in range(world)]
+    gathered = gather_score_tiles(local, counts=counts, timing=timing)
     t3 = time.perf_counter()
     if rank == 0 and place and len(alg.Ds):
         have = [i for i, k in enumerate(keys) if k in alg.Ds]
@@ -314,6 +329,7 @@ def score_tiles(alg, tile_ids, T, tiles=None, lengths=None, place=True):
     t4 = time.perf_counter()
     return {"pairs_local": int(len(mine)), "pairs_total": int(sum(tile_pair_count(alg.N, T, t) for t in sub)),
             "deal_s": t1 - t0, "score_s": t_score, "gather_place_s": t4 - t2, "gather_s": t3 - t2, "place_s": t4 - t3,
+            "gather_wait_s": timing.get("gather_wait_s", 0.0), "gather_d2h_s": timing.get("gather_d2h_s", 0.0),
             "lpt_imbalance": float(load.max() / max(load.mean(), 1e-30)),
             "tiles": len(sub), "keys": keys, "pairs_mine": mine}
 

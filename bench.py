@@ -379,7 +379,7 @@ def run_b200(args, rank, world, local):
         alg.share_songs_allgather(range(s0, s1))
         parallel.score_tiles(alg, ids, TILE, ts.tiles, lengths)
     share_s = gather_s = 0.0
-    parts = {"deal_s": 0.0, "score_s": 0.0, "gather_s": 0.0, "place_s": 0.0}
+    parts = {"deal_s": 0.0, "score_s": 0.0, "gather_s": 0.0, "gather_wait_s": 0.0, "gather_d2h_s": 0.0, "place_s": 0.0}
     e2e_pairs = 0
     barrier()
     t1 = time.perf_counter()
