@@ -48,7 +48,6 @@ constexpr int64_t kMaxChunkNbBytes = (int64_t)6 << 30;     // 6 GiB of nibble-by
 constexpr int64_t kMaxWaveTmatDoubles = (int64_t)4 << 30;  // 32 GiB of T matrices per wave of the tiled long-song sweep
 constexpr int kCounterSlots = 96;
 constexpr int kG6Buckets = kS6Buckets;  // gen-6 launch buckets: CTAs of 128, 256, 512, 640 threads
-constexpr int kFirstChunkPairs = 16384;         // acoss_serra09_pairs: size of the first chunk of a long pair list
 constexpr int kG4Buckets = kS4MaxWarps;            // gen-4 sweep: bucket b = b + 1 warps
 constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) threads, up to 128 * (b + 1) columns
 
@@ -1012,10 +1011,7 @@ int acoss_serra09_pairs(acoss_ctx* c, const int32_t* pairs, int64_t P, int32_t m
     auto cut = [&](int64_t p0) {
         int n = 0;
         int64_t sep = 0, crp = 0, nbb = 0;
-        // the first chunk of a long list is small: its preparation is the only one no kernel hides
-        const int limit = (p0 == 0 && P > 4 * (int64_t)kFirstChunkPairs) ? std::min(c->opt_chunk_pairs, kFirstChunkPairs)
-                                                                          : c->opt_chunk_pairs;
-        while (p0 + n < P && n < limit) {
+        while (p0 + n < P && n < c->opt_chunk_pairs) {
             const int Li = c->h_len[pairs[2 * (p0 + n)]], Lj = c->h_len[pairs[2 * (p0 + n) + 1]];
             const int64_t M = std::max(Li - m + 1, 0), N = std::max(Lj - m + 1, 0);
             const int64_t s2 = M + N, c2 = std::max(M, N) * ((std::min(M, N) + 31) / 32 + 1);
