@@ -73,6 +73,8 @@ def parse_args():
     ap.add_argument("--all-pairs", action="store_true",
                     help="--impl reference: one step = every unique pair of the set (covers80: 12 720), not a sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pair-order", choices=("tiles", "shuffled", "ascending"), default="tiles",
+                    help="experiment: order of a rank's pair list inside the value region (tiles = as dealt, most expensive tiles first)")
     ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
                     help="library tuning knob for A/B runs (acoss_set_option), e.g. --opt dp_packed=0")
     ap.add_argument("--mfcc", action="store_true", help="also time the default plugin call (chroma + mfcc halves) once")
@@ -348,6 +350,9 @@ def run_b200(args, rank, world, local):
     for s in range(args.warmup):
         ctx.serra09_pairs(ts.rank_pairs(s, world, rank)[0], m=M_WIN, kappa=KAPPA)
     batches = [ts.rank_pairs(args.warmup + s, world, rank) for s in range(args.steps)]
+    if args.pair_order != "tiles":
+        rng = np.random.default_rng(99)
+        batches = [(p[rng.permutation(len(p))] if args.pair_order == "shuffled" else p[::-1], n, im) for p, n, im in batches]
     total_pairs = sum(b[1] for b in batches)
     imbalance = float(np.mean([b[2] for b in batches]))
     sampler = ClockSampler(local)
