@@ -63,7 +63,6 @@ SIGNATURES = {
     "acoss_last_stage_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_debug_host_ms": (ctypes.c_int, [ctypes.c_void_p, _c_f32p]),
     "acoss_last_aggregate_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]),
-    "acoss_debug_sweep6_cycles": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
     "acoss_upload_aux_songs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int32]),
     "acoss_snf_pairs": (ctypes.c_int, [ctypes.c_void_p, _c_i32p, ctypes.c_int64, ctypes.c_int32, ctypes.c_double, ctypes.c_int32,
                                        ctypes.c_uint32, _c_f32p, _c_f32p, _c_i32p, _c_i32p, _c_f64p, _c_i64p, _c_u32p, _c_i64p]),

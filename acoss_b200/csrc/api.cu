@@ -23,8 +23,6 @@
 #include "kernels_sweep1t.cuh"
 #include "kernels_sweep2.cuh"
 #include "kernels_sweep4.cuh"
-#include "kernels_sweep5.cuh"
-#include "kernels_sweep6.cuh"
 #include "kernels_feat.cuh"
 #include "kernels_eval.cuh"
 
@@ -47,7 +45,6 @@ constexpr int64_t kMaxChunkCrpWords = (int64_t)1 << 30;    // 4 GiB
 constexpr int64_t kMaxChunkNbBytes = (int64_t)6 << 30;     // 6 GiB of nibble-byte CRPs (gen 4)
 constexpr int64_t kMaxWaveTmatDoubles = (int64_t)4 << 30;  // 32 GiB of T matrices per wave of the tiled long-song sweep
 constexpr int kCounterSlots = 96;
-constexpr int kG6Buckets = kS6Buckets;  // gen-6 launch buckets: CTAs of 128, 256, 512, 640 threads
 constexpr int kG4Buckets = kS4MaxWarps;            // gen-4 sweep: bucket b = b + 1 warps
 constexpr int kFastBuckets = kFastMaxCols / 128;  // bucket b: T = 32 * (b + 1) threads, up to 128 * (b + 1) columns
 
@@ -62,8 +59,6 @@ struct ItemLists {
     std::vector<uint32_t> te;                                        // pairs whose CRP comes from the stored T matrix
     int te_rows = 0;
     std::vector<uint32_t> g4_0[kG4Buckets], g4_2[kG4Buckets];    // gen-4 sweep: separators / CRP
-    std::vector<uint32_t> g6_0[kS6Buckets], g6_2[kS6Buckets];  // gen-6 (DMMA) sweep by CTA size
-    std::vector<uint32_t> g5_0[2], g5_2[2];                          // gen-5 sweep, 4 / 8 compute warps
     std::vector<uint32_t> g4_pack;                                   // pairs whose nibble CRP needs packing
     std::vector<uint32_t> g7_0[kSweep7Buckets], g7_2[kSweep7Buckets];  // gen-7 sweep by column capacity
     bool have_keys = false;                                          // some pair uses the integer-key sweeps
@@ -83,7 +78,7 @@ struct ChunkPlan {
     size_t n_items = 0, pw_bytes = 0, res_off = 0;   // res_off: float results [q | d | sw] of n each in the staging image
     PinBuf* stage = nullptr;
     size_t o_fast0[kFastBuckets], o_fast2[kFastBuckets], o_wide0, o_wide1, o_dp4, o_dp8, o_dp16;
-    size_t o_g40[kG4Buckets], o_g42[kG4Buckets], o_g4pack, o_g50[2], o_g52[2], o_g60[kG6Buckets], o_g62[kG6Buckets];
+    size_t o_g40[kG4Buckets], o_g42[kG4Buckets], o_g4pack;
     size_t o_g70[kSweep7Buckets], o_g72[kSweep7Buckets], o_t3, o_tsel, o_t1, o_te;
 };
 
@@ -306,78 +301,6 @@ int launch_emit_crp(acoss_ctx* c, const uint32_t* d_items, int n_items, int max_
     return ACOSS_OK;
 }
 
-template <int MODE>
-int launch_sweep5(acoss_ctx* c, const uint32_t* d_items, int n_items, int nwg, int m, unsigned int* d_counter, uint32_t flags) {
-    if (n_items <= 0) return ACOSS_OK;
-    auto kfn = (nwg == 1) ? k_sweep5<12, MODE, 9, 1> : k_sweep5<12, MODE, 9, 2>;
-    const int threads = 256 * nwg;
-    const size_t smem = (size_t)s5_layout(4 * nwg, m, 12).total;
-    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, threads, smem));
-    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep5 cannot be resident (threads %d, smem %zu B)", threads, smem);
-    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
-    Sweep4Args A;
-    memset(&A, 0, sizeof(A));
-    A.frames = c->frames.as<double>();
-    A.wnorm = c->wnorm.as<double>();
-    A.offs = c->offs.as<int64_t>();
-    A.pairs = c->pairs.as<PairWork>();
-    A.items = d_items;
-    A.n_items = n_items;
-    A.counter = d_counter;
-    A.sepk = c->sepk.as<int32_t>();
-    A.sepx = c->sepx.as<double>();
-    A.nb = c->nb.as<uint8_t>();
-    A.m = m;
-    A.gap = c->opt_gap;
-    A.flags = flags;
-    ACOSS_LAUNCH(kfn, grid, threads, smem, c->stream, A);
-    c->launches++;
-    CU(cudaGetLastError());
-    return ACOSS_OK;
-}
-
-template <int MODE>
-int launch_sweep6(acoss_ctx* c, const uint32_t* d_items, int n_items, int bucket, int m, unsigned int* d_counter, uint32_t flags) {
-    if (n_items <= 0) return ACOSS_OK;
-    int threads = 0;
-    void (*kfn)(Sweep4Args) = nullptr;
-    switch (bucket) {
-        case 0: kfn = k_sweep6<MODE, 9, 128>; threads = 128; break;
-        case 1: kfn = k_sweep6<MODE, 9, 256>; threads = 256; break;
-        case 2: kfn = k_sweep6<MODE, 9, 512>; threads = 512; break;
-        case 3: kfn = k_sweep6<MODE, 9, 640>; threads = 640; break;
-        default: return fail(ACOSS_ERR_ARG, "k_sweep6: no kernel for bucket %d", bucket);
-    }
-    const size_t smem = (size_t)s6_layout(threads, 12).total;
-    CU(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kfn, threads, smem));
-    if (occ < 1) return fail(ACOSS_ERR_CUDA, "k_sweep6 cannot be resident (threads %d, smem %zu B)", threads, smem);
-    const int grid = (int)std::min<int64_t>((int64_t)n_items, (int64_t)c->sm_count * occ);
-    Sweep4Args A;
-    memset(&A, 0, sizeof(A));
-    A.frames = c->frames.as<double>();
-    A.wnorm = c->wnorm.as<double>();
-    A.norms = c->norms.as<double>();
-    A.offs = c->offs.as<int64_t>();
-    A.pairs = c->pairs.as<PairWork>();
-    A.items = d_items;
-    A.n_items = n_items;
-    A.counter = d_counter;
-    A.sepk = c->sepk.as<int32_t>();
-    A.sepx = c->sepx.as<double>();
-    A.nb = c->nb.as<uint8_t>();
-    A.m = m;
-    A.gap = c->opt_gap;
-    A.flags = flags;
-    ACOSS_LAUNCH(kfn, grid, threads, smem, c->stream, A);
-    c->launches++;
-    CU(cudaGetLastError());
-    return ACOSS_OK;
-}
-
 template <int CPL>
 int launch_dp(acoss_ctx* c, const uint32_t* d_items, int n_items, uint32_t flags, float* q, float* d, float* sw,
               bool packed_ok) {
@@ -504,36 +427,18 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
             if (keys12 || keys7) {
                 L.have_keys = true;
                 const int own4 = s4_own_cols(m);
-                const bool g5 = c->opt_sweep_gen >= 5 && m == 9;  // the warp-specialised kernels are built for m = 9
                 const int b0 = (Lc_of(other) - 1) / own4, b2 = (Lc_of(dpo) - 1) / own4;  // compute warps needed - 1
-                // gen 6 (DMMA) per orientation where the column song fits its largest CTA
-                const bool g6 = c->opt_sweep_gen >= 6 && m == 9 &&
-                                (size_t)s6_layout(512, BINS).total <= (size_t)c->max_smem - 1024;
-                auto use6 = [&](int Lc) { return g6 && Lc <= kS6MaxThreads - kS6Pad; };
                 if (!(nonmutual && dpo == 0)) {
                     if (b7(Lc_of(other)) >= 0)
                         L.g7_0[b7(Lc_of(other))].push_back((uint32_t)p * 2 + other);
-                    else if (use6(Lc_of(other)))
-                        L.g6_0[s6_bucket_of(s6_threads_for(Lc_of(other)))].push_back((uint32_t)p * 2 + other);
-                    else if (g5 && b0 < 8)
-                        L.g5_0[b0 / 4].push_back((uint32_t)p * 2 + other);
                     else
                         L.g4_0[b0].push_back((uint32_t)p * 2 + other);
                 }
                 if (b7(Lc_of(dpo)) >= 0) {
                     L.g7_2[b7(Lc_of(dpo))].push_back((uint32_t)p);  // writes packed CRP words itself
                 } else {
-                    if (use6(Lc_of(dpo))) {
-                        const int t2 = s6_threads_for(Lc_of(dpo));
-                        L.g6_2[s6_bucket_of(t2)].push_back((uint32_t)p);
-                        w.nb_stride = t2 / 4;
-                    } else if (g5 && b2 < 8) {
-                        L.g5_2[b2 / 4].push_back((uint32_t)p);
-                        w.nb_stride = 128 * (b2 / 4 + 1);
-                    } else {
-                        L.g4_2[b2].push_back((uint32_t)p);
-                        w.nb_stride = 32 * (b2 + 1);
-                    }
+                    L.g4_2[b2].push_back((uint32_t)p);
+                    w.nb_stride = 32 * (b2 + 1);
                     L.g4_pack.push_back((uint32_t)p);
                     w.nb_off = nb_total;
                     nb_total += ((int64_t)w.crp_rows * w.nb_stride + 15) & ~(int64_t)15;
@@ -603,8 +508,6 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
                      L.t3.size() + L.tsel.size() + L.t1.size() + L.te.size();
     for (int b = 0; b < kFastBuckets; ++b) n_items += L.fast0[b].size() + L.fast2[b].size();
     for (int b = 0; b < kG4Buckets; ++b) n_items += L.g4_0[b].size() + L.g4_2[b].size();
-    for (int b = 0; b < 2; ++b) n_items += L.g5_0[b].size() + L.g5_2[b].size();
-    for (int b = 0; b < kG6Buckets; ++b) n_items += L.g6_0[b].size() + L.g6_2[b].size();
     for (int b = 0; b < kSweep7Buckets; ++b) n_items += L.g7_0[b].size() + L.g7_2[b].size();
     // stage: [PairWork...][items...]
     const size_t pw_bytes = (size_t)n * sizeof(PairWork);
@@ -636,10 +539,6 @@ int prep_chunk(acoss_ctx* c, const int32_t* pairs, int64_t p0, int n, int m, dou
     for (int b = 0; b < kG4Buckets; ++b) P.o_g40[b] = put(L.g4_0[b]);
     for (int b = 0; b < kG4Buckets; ++b) P.o_g42[b] = put(L.g4_2[b]);
     P.o_g4pack = put(L.g4_pack);
-    for (int b = 0; b < 2; ++b) P.o_g50[b] = put(L.g5_0[b]);
-    for (int b = 0; b < 2; ++b) P.o_g52[b] = put(L.g5_2[b]);
-    for (int b = 0; b < kG6Buckets; ++b) P.o_g60[b] = put(L.g6_0[b]);
-    for (int b = 0; b < kG6Buckets; ++b) P.o_g62[b] = put(L.g6_2[b]);
     for (int b = 0; b < kSweep7Buckets; ++b) P.o_g70[b] = put(L.g7_0[b]);
     for (int b = 0; b < kSweep7Buckets; ++b) P.o_g72[b] = put(L.g7_2[b]);
     P.n_items = n_items;
@@ -753,19 +652,11 @@ int exec_chunk(acoss_ctx* c, ChunkPlan& P, int m, uint32_t flags, const float* q
     }
     for (int b = kSweep7Buckets - 1; b >= 0; --b)
         if ((rc = acoss_launch_sweep7(c, 0, BINS, d_items + P.o_g70[b], (int)L.g7_0[b].size(), b, d_cnt + 80 + b, flags))) return rc;
-    for (int b = kG6Buckets - 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep6<0>(c, d_items + P.o_g60[b], (int)L.g6_0[b].size(), b, m, d_cnt + 64 + b, flags))) return rc;
-    for (int b = 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep5<0>(c, d_items + P.o_g50[b], (int)L.g5_0[b].size(), b + 1, m, d_cnt + 56 + b, flags))) return rc;
     for (int b = kG4Buckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep4<12, 0>(c, d_items + P.o_g40[b], (int)L.g4_0[b].size(), b, m, d_cnt + 32 + b, flags))) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
     for (int b = kSweep7Buckets - 1; b >= 0; --b)
         if ((rc = acoss_launch_sweep7(c, 2, BINS, d_items + P.o_g72[b], (int)L.g7_2[b].size(), b, d_cnt + 80 + kSweep7Buckets + b, flags))) return rc;
-    for (int b = kG6Buckets - 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep6<2>(c, d_items + P.o_g62[b], (int)L.g6_2[b].size(), b, m, d_cnt + 64 + kG6Buckets + b, flags))) return rc;
-    for (int b = 1; b >= 0; --b)
-        if (BINS == 12 && (rc = launch_sweep5<2>(c, d_items + P.o_g52[b], (int)L.g5_2[b].size(), b + 1, m, d_cnt + 58 + b, flags))) return rc;
     for (int b = kG4Buckets - 1; b >= 0; --b)
         if (BINS == 12 && (rc = launch_sweep4<12, 2>(c, d_items + P.o_g42[b], (int)L.g4_2[b].size(), b, m, d_cnt + 32 + kG4Buckets + b, flags))) return rc;
     if (!L.g4_pack.empty()) {
@@ -1596,7 +1487,7 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
     else if (n == "tiled_wide")
         c->opt_tiled_wide = value != 0;
     else if (n == "sweep_gen") {
-        if (value < 2 || value > 7 || value == 3) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2, 4, 5, 6 or 7");
+        if (value != 2 && value != 4 && value != 7) return fail(ACOSS_ERR_ARG, "sweep_gen must be 2, 4 or 7");
         c->opt_sweep_gen = (int)value;
     } else if (n == "gap_units") {
         if (value < 2 || value > (1 << 24)) return fail(ACOSS_ERR_ARG, "gap_units must be in [2, 2^24]");
@@ -1621,29 +1512,6 @@ int acoss_set_option(acoss_ctx* c, const char* name, int64_t value) {
 int64_t acoss_kernel_launches(acoss_ctx* c) { return c ? c->launches : 0; }
 void acoss_reset_counters(acoss_ctx* c) {
     if (c) c->launches = 0;
-}
-
-/* Profiling aid, not part of the drop-in surface: cycle counters of k_sweep6 (debug flag bit 26),
- * summed over every warp: [0] stage 2, [1] selection, [2] stage 1, [3] barrier wait, [4] periods (per CTA),
- * [5] items.  reset != 0 clears them.  All zero unless the library was built with -DACOSS_S6_PROFILE
- * (ACOSS_NVCC_DEFINES=ACOSS_S6_PROFILE python -m acoss_b200.build --force). */
-int acoss_debug_sweep6_cycles(acoss_ctx* c, uint64_t out[8], int reset) {
-    if (!c || !out) return fail(ACOSS_ERR_ARG, "null argument");
-#if ACOSS_S6_PROF
-    CU(cudaSetDevice(c->device));
-    CU(cudaStreamSynchronize(c->stream));
-    unsigned long long h[8];
-    CU(cudaMemcpyFromSymbol(h, g_s6_prof, sizeof(h)));
-    for (int i = 0; i < 8; ++i) out[i] = h[i];
-    if (reset) {
-        memset(h, 0, sizeof(h));
-        CU(cudaMemcpyToSymbol(g_s6_prof, h, sizeof(h)));
-    }
-#else
-    for (int i = 0; i < 8; ++i) out[i] = 0;
-    (void)reset;
-#endif
-    return ACOSS_OK;
 }
 
 int acoss_debug_sweep7_stats(acoss_ctx* c, uint64_t out[16], int reset) {

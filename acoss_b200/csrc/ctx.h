@@ -124,15 +124,12 @@ struct acoss_ctx {
                                  // 128-column blocks at 80 registers (6 CTAs/SM) beat wider lanes
     int opt_dp_packed = 1;       // Qmax + Dmax on packed 16-bit lanes (k_dp16) where the plots are small enough; 0: k_dp
     int opt_chunk_pairs = 1 << 18;
-    int opt_sweep_gen = 7;         // 7 (default): lane-group selection + packed CRP from the sweep (kernels_sweep7.cuh)
-                                   // for every orientation whose column song has <= 1015 frames (m = 9, 12 / 13
-                                   // bins), the rest as 6;
-                                   // 6: DMMA sweep (kernels_sweep6.cuh) for every orientation whose column
-                                   // song has <= 631 frames (m = 9, 12 bins), the rest as 5;
-                                   // 5: warp-specialised integer-key sweep (kernels_sweep5.cuh; falls back
-                                   // to 4 for windows other than 9 and column songs over 960 frames);
-                                   // 4: integer-key sweep (kernels_sweep4.cuh); 2: float64-selection sweep
-                                   // (kernels_sweep2.cuh)
+    int opt_sweep_gen = 7;         // 7 (default): FP64 tensor-core sweep with chained row selection and packed CRP output
+                                   // (kernels_sweep7.cuh) for every orientation whose column song has <= 1015 frames
+                                   // (m = 9, 12 / 13 bins), the rest as 4; 4: integer-key SIMT sweep
+                                   // (kernels_sweep4.cuh, 12 bins, column songs of up to 1320 frames), the rest as 2;
+                                   // 2: float64-selection sweep (kernels_sweep2.cuh).  Generations 3, 5 and 6 are
+                                   // retired to profiles/exp/.
     int opt_gap = 2;               // gen 4: safety gap G in key units (tests raise it to exercise the exact path)
     int opt_single_stream = 0;     // 1: no side stream (profiling / debugging)
     int opt_eval_direct = 0;       // 1: cliques of more than 5 songs through the one-compare-per-member rank kernel

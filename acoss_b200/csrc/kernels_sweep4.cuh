@@ -59,7 +59,7 @@ constexpr int32_t kKeyInf = 0x7fffffff;
 struct Sweep4Args {
     const double* frames;   // [total_frames][BINS]
     const double* wnorm;    // [total_frames] windowed squared norms: sum of the m frames ending here
-    const double* norms;    // [total_frames] squared norms of the frames (gen 6)
+    const double* norms;    // [total_frames] squared norms of the frames (gen 6, retired)
     const int64_t* offs;
     const PairWork* pairs;
     const uint32_t* items;  // MODE 0: pair*2 + orientation; MODE 2: pair

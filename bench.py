@@ -69,7 +69,7 @@ def parse_args():
     ap.add_argument("--cpu-pairs", type=int, default=0,
                     help="pairs of the CPU sample (0: 800 per core in the default arm = 15-25 s of CPU work, "
                          "150 per core and step in the reference arm)")
-    ap.add_argument("--sweep-gen", type=int, default=0, help="force a sweep generation (2, 4 .. 7); 0 = library default")
+    ap.add_argument("--sweep-gen", type=int, default=0, help="force a sweep generation (2, 4 or 7); 0 = library default")
     ap.add_argument("--all-pairs", action="store_true",
                     help="--impl reference: one step = every unique pair of the set (covers80: 12 720), not a sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -659,8 +659,8 @@ def finish_b200(v):
                      "kernel": ("k_sweep_tile + k_select_rows_cta + k_emit_crp (tiled long-song sweep, float64 SIMT, windowed "
                                 "distances through HBM)") if args.config == "stress" else
                                "k_sweep7 (FP64 tensor-core dot products + integer window sums + chained row selection: "
-                               "separators of one orientation, packed CRP of the other); k_sweep6/5/4 only for column "
-                               "songs over 1015 frames",
+                               "separators of one orientation, packed CRP of the other); k_sweep4 / k_sweep_fast / the tiled kernels only "
+                               "for column songs over 1015 frames",
                      "note": "FP64 roofline, NOT the bf16 figure of MEASURED_PEAKS.json (which has no FP64 entry): "
                              "peak = 148 SM x 64 FP64 FMA/cycle x 2 x sm_max_mhz, the rate measured for both DMMA "
                              "(mma.sync.m8n8k4.f64, profiles/exp/ubench/dmma_rate.cu) and DFMA; algorithmic 26 flop/cell "

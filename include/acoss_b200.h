@@ -238,9 +238,9 @@ int acoss_bind_score_matrices(acoss_ctx* ctx, float* qmax_dev, float* dmax_dev, 
 /* Test / tuning knobs (results never depend on them): "force_wide_sweep" (0/1),
  * "force_gscratch" (0/1), "dp_max_cpl" (4, 8, 16), "dp_packed" (0/1: Qmax + Dmax on packed 16-bit lanes, default 1),
  * "chunk_pairs" (pairs per internal chunk),
- * "sweep_gen" (2 .. 6: which generation of the cross-similarity sweep runs where it applies;
- * default 6 = FP64 tensor-core sweep for column songs of up to 631 frames, warp-specialised
- * SIMT sweep up to 960, integer-key SIMT sweep up to 1320, general sweeps beyond),
+ * "sweep_gen" (2, 4 or 7: which generation of the cross-similarity sweep runs where it applies; default 7 = FP64
+ * tensor-core sweep with chained row selection for column songs of up to 1015 frames, integer-key SIMT sweep (4) up to
+ * 1320, float64 sweeps (2) beyond; 4 and 2 force the older kernels for cross-checks),
  * "eval_direct" (0/1, default 0: acoss_eval_ranks counts cliques of more than 5 songs with one compare per member
  * instead of the binary search + histogram kernel),
  * "tiled_wide" (0/1, default 1: column songs beyond 1408 frames go through the tiled float64 sweep,
@@ -249,9 +249,6 @@ int acoss_bind_score_matrices(acoss_ctx* ctx, float* qmax_dev, float* dmax_dev, 
  * float64; larger values only move work to the exact path), "single_stream" (0/1: keep the
  * long-song sweeps on the main stream), "debug_flags" (profiling experiments). */
 int acoss_set_option(acoss_ctx* ctx, const char* name, int64_t value);
-
-/* Profiling aid (not part of the drop-in surface): cycle counters of the gen-6 sweep, see api.cu. */
-int acoss_debug_sweep6_cycles(acoss_ctx* ctx, uint64_t out[8], int reset);
 
 /* Profiling aid: counters of the gen-7 sweep, summed over all launches: [0] rows resolved, [1] rows decided in
  * float64, [2] strips, [3] items, [4..15] cycles per phase (kernels_sweep7.cuh).  All zero unless the library was
