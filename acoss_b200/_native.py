@@ -80,8 +80,17 @@ def _ptr(arr, typ):
     return None if arr is None else arr.ctypes.data_as(typ)
 
 
+_SHIPPED_LIB = DEFAULT_LIB
+
+
 def load_library(path: str | None = None) -> ctypes.CDLL:
     path = path or DEFAULT_LIB
+    # Only the CUDA library built in-tree is the product.  tests/ also load the same kernel sources compiled for the
+    # host against a SIMT emulator (tests/emu/); that build is test infrastructure, never a fallback, and loading any
+    # library other than the shipped one needs the explicit opt-in that tests/conftest.py sets.
+    if os.path.realpath(path) != os.path.realpath(_SHIPPED_LIB) and os.environ.get("ACOSS_B200_ALLOW_TEST_LIB") != "1":
+        raise AcossError("refusing to load %s: only %s is the product library (set ACOSS_B200_ALLOW_TEST_LIB=1 in "
+                         "tests that load the emulator build)" % (path, _SHIPPED_LIB))
     if not os.path.exists(path):
         raise AcossError("native library %s not found: build it with `python -m acoss_b200.build` "
                          "(there is no CPU fallback)" % path)

@@ -9,6 +9,9 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GOLDEN = os.path.join(ROOT, "tests", "golden", "serra09_golden.npz")
+# the CPU tests step the kernel sources under the SIMT emulator (tests/emu/): acoss_b200._native refuses any library
+# but the shipped CUDA one without this opt-in (inherited by the torchrun subprocesses of test_parallel.py)
+os.environ.setdefault("ACOSS_B200_ALLOW_TEST_LIB", "1")
 
 
 def pytest_configure(config):

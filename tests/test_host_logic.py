@@ -207,3 +207,14 @@ def test_hdf5_chunked_gzip_shuffle_roundtrip_and_filters(tmp_path):
     r = hdf5io._Reader(np.memmap(path, dtype=np.uint8, mode="r"))
     with pytest.raises(NotImplementedError, match="blosc.*re-export"):
         r.read_chunked(struct.pack("<BBB", 3, 2, 2) + struct.pack("<Q", 0) + struct.pack("<II", 4, 4), np.dtype("f4"), (8,), [32001])
+
+
+def test_only_the_shipped_library_loads_without_opt_in(monkeypatch, tmp_path):
+    """acoss_b200._native refuses a library other than the in-tree CUDA build unless the test opt-in is set: the
+    emulator build can never be picked up as a fallback."""
+    from acoss_b200 import _native
+    monkeypatch.delenv("ACOSS_B200_ALLOW_TEST_LIB", raising=False)
+    other = tmp_path / "libother.so"
+    other.write_bytes(b"")
+    with pytest.raises(_native.AcossError, match="refusing to load"):
+        _native.load_library(str(other))
