@@ -249,6 +249,7 @@ int launch_select_rows(acoss_ctx* c, const uint32_t* d_items, int n_items, int m
     A.tmat = c->tmat.as<double>();
     A.seps = c->seps.as<double>();
     A.m = m;
+    A.flags = c->opt_debug_flags;
     if (max_cols <= 32 * kSelThreads) {
         // the row fits the registers of one CTA: CTA-per-row selection
         A.row_blocks = (max_rows + kSelRowsPerCta - 1) / kSelRowsPerCta;
@@ -350,7 +351,7 @@ int dp_cpl(const acoss_ctx* c, int cols) {
 }
 
 void classify_dp(const acoss_ctx* c, ItemLists& L, uint32_t p, int rows, int cols) {
-    if (rows + cols > kDp16MaxSide) L.dp_packed_ok = false;
+    if (rows + cols > kDp16MaxSide || cols > kDp16MaxCols) L.dp_packed_ok = false;
     const int cpl = dp_cpl(c, cols);
     (cpl == 4 ? L.dp4 : (cpl == 8 ? L.dp8 : L.dp16)).push_back(p);
 }

@@ -23,6 +23,8 @@
 namespace acoss {
 
 constexpr int kDp16MaxSide = 10000;            // rows + cols of a plot the packed kernel accepts
+constexpr int kDp16MaxCols = 1536;             // wider plots (dozens of column blocks, a hand-over record per row and block) are
+                                               // faster on k_dp: 75 vs 90 ms per step of the long-song stress set
 constexpr unsigned kDp16Neg = 0x0000C000u;     // (-16384, 0): Qmax lane of the Dmax-only addends
 
 #ifdef ACOSS_EMU

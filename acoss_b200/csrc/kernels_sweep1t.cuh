@@ -242,6 +242,7 @@ struct SelArgs {
     double* seps;
     int m;
     int stage_cols;         // > 0: dynamic shared memory holds kSelWarps rows of this many doubles
+    uint32_t flags;         // debug: bit 23 = no secant steps in k_select_rows_cta (A/B)
 };
 constexpr int kSelWarps = 4;
 constexpr int kSelRowsPerWarp = 8;
@@ -332,6 +333,7 @@ __global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
     int pc = 0, pm = 0;
     const double NANV = __longlong_as_double(0x7ff8000000000000LL);
     double guess = NANV;  // no guess yet
+    double slope = 0.0;   // distance per rank near the separator, carried from row to row
     const int i0 = rb * kSelRowsPerCta;
     for (int i = i0; i < imin(i0 + kSelRowsPerCta, Mo); ++i) {
         const double* row = tm + (int64_t)i * No;
@@ -368,21 +370,40 @@ __global__ void __launch_bounds__(kSelThreads) k_select_rows_cta(SelArgs A) {
                 bool found = (clo == k);
                 if (!found) {
                     const bool use_guess = (guess > lo) && (guess < hi);
+                    // Secant steps on the LOCAL slope (distance per rank around the separator: from the last two
+                    // counts of this row, else carried over from the previous row) before the bracket-wide
+                    // interpolation: the values of a row are far from uniform between its minimum and maximum, so
+                    // interpolating over the whole bracket needs ~7 counting passes where the local slope needs ~3.
+                    double tp = 0.0, tpp = 0.0;   // thresholds of the last two counting passes of this row
+                    int cp = -1, cpp = -1;        // and their counts
                     for (int iter = 0; iter < 400 && !found; ++iter) {
                         if (iter == 0 && use_guess) {
                             t = guess;
                         } else {
-                            if (iter & 1)
-                                t = 0.5 * lo + 0.5 * hi;
-                            else
-                                // the fraction only steers the search: single precision is plenty
-                                t = lo + (hi - lo) * (double)((float)(k - clo) * __frcp_rn((float)(chi - clo)));
-                            if (!(t > lo && t < hi)) {
-                                t = 0.5 * lo + 0.5 * hi;
-                                if (!(t > lo && t < hi)) break;  // bracket collapsed: exact ties
+                            double tn = NANV;
+                            if (!(A.flags & (1u << 23)) && iter < 6 && cp >= 0) {
+                                if (cpp >= 0 && cp != cpp) slope = (tp - tpp) / (double)(cp - cpp);
+                                if (slope > 0.0) tn = tp + ((double)(k - cp) + 0.5) * slope;
+                            }
+                            if (tn > lo && tn < hi) {
+                                t = tn;
+                            } else {
+                                if (iter & 1)
+                                    t = 0.5 * lo + 0.5 * hi;
+                                else
+                                    // the fraction only steers the search: single precision is plenty
+                                    t = lo + (hi - lo) * (double)((float)(k - clo) * __frcp_rn((float)(chi - clo)));
+                                if (!(t > lo && t < hi)) {
+                                    t = 0.5 * lo + 0.5 * hi;
+                                    if (!(t > lo && t < hi)) break;  // bracket collapsed: exact ties
+                                }
                             }
                         }
                         const int c = count_le(t);
+                        tpp = tp;
+                        cpp = cp;
+                        tp = t;
+                        cp = c;
                         if (c == k) {
                             found = true;
                         } else if (c < k) {
