@@ -32,6 +32,14 @@
  *                           (benchmarking/Serra09.py:24-28, 96-114)
  *   acoss_eval_ranks        the sort + rank loop of CoverAlgorithm.getEvalStatistics
  *                           (benchmarking/CoverAlgorithm.py:345-382)
+ *   acoss_bind_score_matrices
+ *                           the `self.Ds[type][i, j] = score` side effect of Serra09.similarity and the
+ *                           `Ds += Ds.T` of all_pairwise (benchmarking/Serra09.py:174-175, 181-184;
+ *                           CoverAlgorithm.py:180-182), kept in device memory for acoss_eval_ranks
+ *
+ * Without a counterpart in the reference: acoss_dp_packed_static (see below), the measurement
+ * aids acoss_last_stage_ms / acoss_last_eval_ms / acoss_last_aggregate_stats / acoss_kernel_launches and the
+ * profiling aids acoss_debug_*.
  */
 #ifndef ACOSS_B200_H
 #define ACOSS_B200_H
