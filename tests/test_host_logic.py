@@ -218,3 +218,22 @@ def test_only_the_shipped_library_loads_without_opt_in(monkeypatch, tmp_path):
     other.write_bytes(b"")
     with pytest.raises(_native.AcossError, match="refusing to load"):
         _native.load_library(str(other))
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py --impl reference (the CPU arm the driver runs beside the GPU arm): one JSON line on stdout with the
+    contract's keys, on a tiny sample so that it runs in seconds here."""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--config", "covers80",
+                        "--cpu-pairs", "24", "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "song_pairs_per_sec" and d["unit"] == "pairs/s"
+    assert d["value"] > 0 and d["higher_is_better"] is True and d["steps"] == 1
+    assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"] == {"value": d["value"], "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["config"]["songs"] == 160 and d["config"]["m"] == 9
