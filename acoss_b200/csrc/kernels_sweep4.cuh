@@ -52,7 +52,10 @@ static __device__ unsigned long long g_s4_sel_stats[8];
 
 constexpr int kS4Stage = 32;        // rows of the row song per TMA bulk copy
 constexpr int kS4MaxWarps = 11;     // CTAs of up to 352 threads (12 warps fit, measured no faster: profiles/exp/README_r02.md)
-constexpr int kS4EMax = 6;          // ranks walked by the extraction pass
+#ifndef ACOSS_S4_EMAX
+#define ACOSS_S4_EMAX 6
+#endif
+constexpr int kS4EMax = ACOSS_S4_EMAX;   // ranks walked by the extraction pass (A/B builds: -DACOSS_S4_EMAX=n)
 constexpr int kS4MaxFlag = 32;      // flagged columns / patch candidates kept per item / row
 constexpr int32_t kKeyInf = 0x7fffffff;
 
